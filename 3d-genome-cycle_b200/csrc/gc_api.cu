@@ -1,0 +1,1121 @@
+// gc_api.cu -- implementation of the C-ABI in include/gc_b200.h on top of the
+// sm_100a kernels in gc_kernels.cuh / gc_step.cuh / gc_query.cuh.
+//
+// There is NO CPU fallback here: every entry point either runs the CUDA path
+// or fails with GC_ERR_CUDA.
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_reduce.cuh>
+
+#include "../../include/gc_b200.h"
+#include "gc_query.cuh"
+
+using namespace gc;
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+struct HostBond { int i, j, bterm; };
+struct HostTriple { int i, j, k, tterm; };
+struct HostTether { int bead, pole; float spring, length; int term; };
+
+struct gc_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int n = 0, n_rep = 1;
+    std::string error;
+
+    Params hp{};            // host mirror
+    Params *dp = nullptr;   // device copy read by every kernel
+    bool params_dirty = true;
+    bool topo_dirty = true;
+    bool attrs_set = false;
+    int next_term = 0;
+
+    // host-side topology before CSR construction
+    std::vector<HostBond> bonds;
+    std::vector<HostTriple> triples;
+    std::vector<HostTether> tethers;
+    std::vector<int> well_targets;
+
+    // device allocations (freed in gc_destroy)
+    std::vector<void *> allocs;
+    float *d_mob = nullptr;
+    float2 *d_ab = nullptr;
+    int *d_flags = nullptr, *d_bond_off = nullptr, *d_triple_off = nullptr, *d_tether_off = nullptr;
+    BondEntry *d_bond_ent = nullptr;
+    TripleEntry *d_triple_ent = nullptr;
+    TetherEntry *d_tether_ent = nullptr;
+    int *d_well_targets = nullptr;
+    float *d_noise = nullptr;
+    size_t noise_cap = 0;
+    double *d_partials = nullptr;
+    unsigned long long *d_counter = nullptr;
+    void *d_scratch = nullptr;
+    size_t scratch_cap = 0;
+
+    long long run_step = 0;     // host mirror of RepState::step
+    int parity = 0;             // host mirror of RepState::parity (replicas move in lockstep)
+    long long launches = 0;
+    double skin = 0.0;
+    int use_graph = 0;
+
+    // graph cache for the fixed-dt step sequence
+    cudaGraphExec_t graph_exec = nullptr;
+    int graph_steps = 0;
+};
+
+namespace {
+
+int fail(gc_ctx *ctx, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->error = buf;
+    return code;
+}
+
+#define GC_CUDA(ctx, expr)                                                                    \
+    do {                                                                                      \
+        cudaError_t e_ = (expr);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            return fail(ctx, GC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,                     \
+                        cudaGetErrorString(e_), __FILE__, __LINE__);                          \
+        }                                                                                     \
+    } while (0)
+
+#define GC_CHECK_CTX(ctx)                                                                     \
+    do {                                                                                      \
+        if (!(ctx)) return GC_ERR_INVALID;                                                    \
+        cudaError_t e_ = cudaSetDevice((ctx)->device);                                        \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(ctx, GC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e_));       \
+    } while (0)
+
+template<typename T>
+int dev_alloc(gc_ctx *ctx, T **out, size_t count, int fill_byte = 0)
+{
+    void *p = nullptr;
+    size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    GC_CUDA(ctx, cudaMalloc(&p, bytes));
+    GC_CUDA(ctx, cudaMemsetAsync(p, fill_byte, bytes, ctx->stream));
+    ctx->allocs.push_back(p);
+    *out = (T *) p;
+    return GC_OK;
+}
+
+void dev_free(gc_ctx *ctx, void *p)
+{
+    if (!p) return;
+    auto it = std::find(ctx->allocs.begin(), ctx->allocs.end(), p);
+    if (it != ctx->allocs.end()) ctx->allocs.erase(it);
+    cudaFree(p);
+}
+
+template<typename T>
+int upload(gc_ctx *ctx, T **dst, const std::vector<T> &src)
+{
+    if (*dst) dev_free(ctx, *dst);
+    *dst = nullptr;
+    int rc = dev_alloc(ctx, dst, src.size());
+    if (rc) return rc;
+    if (!src.empty()) {
+        GC_CUDA(ctx, cudaMemcpyAsync(*dst, src.data(), src.size() * sizeof(T),
+                                     cudaMemcpyHostToDevice, ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // src may be a temporary
+    }
+    return GC_OK;
+}
+
+dim3 bead_grid(const gc_ctx *ctx, int bs) { return dim3((ctx->n + bs - 1) / bs, ctx->n_rep); }
+
+int new_term(gc_ctx *ctx)
+{
+    if (ctx->next_term >= GC_MAX_TERMS) return fail(ctx, GC_ERR_INVALID, "too many terms");
+    int t = ctx->next_term++;
+    ctx->hp.enabled |= 1u << t;
+    ctx->params_dirty = true;
+    return t;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *gc_version(void) { return "gc_b200 0.1 sm_100a"; }
+
+const char *gc_last_error(const gc_ctx *ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+
+int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
+{
+    if (!out || n_beads < 0 || n_replicas < 1) return GC_ERR_INVALID;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        // Fail loudly: this library has no CPU path.
+        fprintf(stderr, "gc_b200: no CUDA device available (%s)\n",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return GC_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) return GC_ERR_INVALID;
+
+    gc_ctx *ctx = new gc_ctx;
+    ctx->device = device;
+    ctx->n = n_beads;
+    ctx->n_rep = n_replicas;
+    *out = ctx;   // returned even on failure so the caller can read the error
+    GC_CUDA(ctx, cudaSetDevice(device));
+    GC_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+
+    Params &P = ctx->hp;
+    memset(&P, 0, sizeof P);
+    P.n = n_beads;
+    P.n_rep = n_replicas;
+    {
+        long long want = std::max<long long>(8LL * n_beads, 32768);
+        want = std::min<long long>(want, 1LL << 23);
+        P.ncell_max = (int) want;
+    }
+    P.cells_per_cut = 1;
+    if (const char *env = getenv("GC_CELLS_PER_CUT")) P.cells_per_cut = std::max(1, atoi(env));
+    P.skin = 0.0f;
+    P.kT = 1.0f;
+    P.dt = 1.0f;
+    P.pair.mode = PAIR_NONE;
+    P.well.term = -1;
+    P.wall.term = -1;
+
+    size_t RN = (size_t) n_replicas * (size_t) n_beads;
+    int rc = 0;
+    for (int k = 0; k < 2 && !rc; k++) {
+        rc = dev_alloc(ctx, &P.pos[k], RN);
+        if (!rc) rc = dev_alloc(ctx, &P.spos[k], RN);
+    }
+    if (!rc) rc = dev_alloc(ctx, &P.sref, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.sidx, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.scell, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.slot_of, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.sab, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.members, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.cell_of, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.force, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.cell_count, (size_t) n_replicas * P.ncell_max);
+    if (!rc) rc = dev_alloc(ctx, &P.cell_start, (size_t) n_replicas * (P.ncell_max + 1));
+    if (!rc) rc = dev_alloc(ctx, &P.st, (size_t) n_replicas);
+    if (!rc) rc = dev_alloc(ctx, &ctx->dp, 1);
+    if (!rc) rc = dev_alloc(ctx, &ctx->d_partials, (size_t) (n_beads + BS - 1) / BS + 1);
+    if (!rc) rc = dev_alloc(ctx, &ctx->d_counter, 4);
+    if (!rc) rc = dev_alloc(ctx, &ctx->d_mob, (size_t) n_beads);
+    if (!rc) rc = dev_alloc(ctx, &ctx->d_ab, (size_t) n_beads);
+    if (rc) return rc;
+
+    // initial per-replica state
+    std::vector<RepState> st((size_t) n_replicas);
+    for (int r = 0; r < n_replicas; r++) {
+        memset(&st[r], 0, sizeof(RepState));
+        st[r].core_scale = 1.0;
+        st[r].bond_scale = 1.0;
+        st[r].semiaxes[0] = st[r].semiaxes[1] = st[r].semiaxes[2] = 1.0;
+        st[r].seed = 0x9E3779B97F4A7C15ull * (unsigned long long) (r + 1);
+        st[r].need_rebuild = 1;
+    }
+    GC_CUDA(ctx, cudaMemcpyAsync(P.st, st.data(), st.size() * sizeof(RepState),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
+}
+
+int gc_destroy(gc_ctx *ctx)
+{
+    if (!ctx) return GC_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
+    for (void *p : ctx->allocs) cudaFree(p);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// beads
+// ---------------------------------------------------------------------------
+
+int gc_set_bead_attrs(gc_ctx *ctx, const double *mobility, const double *a_factor,
+                      const double *b_factor)
+{
+    GC_CHECK_CTX(ctx);
+    if (!mobility) return fail(ctx, GC_ERR_INVALID, "mobility is required");
+    std::vector<float> mob((size_t) ctx->n);
+    std::vector<float2> ab((size_t) ctx->n);
+    for (int i = 0; i < ctx->n; i++) {
+        mob[i] = (float) mobility[i];
+        ab[i] = make_float2(a_factor ? (float) a_factor[i] : 0.0f,
+                            b_factor ? (float) b_factor[i] : 0.0f);
+    }
+    GC_CUDA(ctx, cudaMemcpyAsync(ctx->d_mob, mob.data(), mob.size() * sizeof(float),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    GC_CUDA(ctx, cudaMemcpyAsync(ctx->d_ab, ab.data(), ab.size() * sizeof(float2),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->hp.mob = ctx->d_mob;
+    ctx->hp.ab = ctx->d_ab;
+    ctx->attrs_set = true;
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+int gc_set_positions_f32(gc_ctx *ctx, int32_t replica, const float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz || replica < -1 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    std::vector<float4> buf((size_t) ctx->n);
+    for (int i = 0; i < ctx->n; i++) {
+        buf[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], 0.0f);
+    }
+    int r0 = replica < 0 ? 0 : replica, r1 = replica < 0 ? ctx->n_rep : replica + 1;
+    for (int r = r0; r < r1; r++) {
+        GC_CUDA(ctx, cudaMemcpyAsync(ctx->hp.pos[ctx->parity] + (size_t) r * ctx->n, buf.data(),
+                                     buf.size() * sizeof(float4), cudaMemcpyHostToDevice,
+                                     ctx->stream));
+    }
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
+}
+
+int gc_set_positions(gc_ctx *ctx, int32_t replica, const double *xyz)
+{
+    if (!ctx || !xyz) return GC_ERR_INVALID;
+    std::vector<float> f((size_t) ctx->n * 3);
+    for (size_t k = 0; k < f.size(); k++) f[k] = (float) xyz[k];
+    return gc_set_positions_f32(ctx, replica, f.data());
+}
+
+int gc_get_positions_f32(gc_ctx *ctx, int32_t replica, float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    std::vector<float4> buf((size_t) ctx->n);
+    GC_CUDA(ctx, cudaMemcpyAsync(buf.data(), ctx->hp.pos[ctx->parity] + (size_t) replica * ctx->n,
+                                 buf.size() * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < ctx->n; i++) {
+        xyz[3 * i] = buf[i].x;
+        xyz[3 * i + 1] = buf[i].y;
+        xyz[3 * i + 2] = buf[i].z;
+    }
+    return GC_OK;
+}
+
+int gc_get_positions(gc_ctx *ctx, int32_t replica, double *xyz)
+{
+    if (!ctx || !xyz) return GC_ERR_INVALID;
+    std::vector<float> f((size_t) ctx->n * 3);
+    int rc = gc_get_positions_f32(ctx, replica, f.data());
+    if (rc) return rc;
+    for (size_t k = 0; k < f.size(); k++) xyz[k] = (double) f[k];
+    return GC_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// read-modify-write of the per-replica state from the host
+template<typename Fn>
+int modify_states(gc_ctx *ctx, int replica, Fn fn)
+{
+    if (replica < -1 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad replica");
+    std::vector<RepState> st((size_t) ctx->n_rep);
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    GC_CUDA(ctx, cudaMemcpy(st.data(), ctx->hp.st, st.size() * sizeof(RepState),
+                            cudaMemcpyDeviceToHost));
+    int r0 = replica < 0 ? 0 : replica, r1 = replica < 0 ? ctx->n_rep : replica + 1;
+    for (int r = r0; r < r1; r++) fn(st[r], r);
+    GC_CUDA(ctx, cudaMemcpy(ctx->hp.st, st.data(), st.size() * sizeof(RepState),
+                            cudaMemcpyHostToDevice));
+    return GC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int gc_set_seeds(gc_ctx *ctx, const uint64_t *seeds)
+{
+    GC_CHECK_CTX(ctx);
+    if (!seeds) return fail(ctx, GC_ERR_INVALID, "seeds is null");
+    return modify_states(ctx, -1, [&](RepState &st, int r) { st.seed = seeds[r]; });
+}
+
+// ---------------------------------------------------------------------------
+// terms
+// ---------------------------------------------------------------------------
+
+int gc_add_pair_softcore_ab(gc_ctx *ctx, double eps_a, double sigma_a, double eps_b,
+                            double sigma_b, int32_t scale_by_core)
+{
+    GC_CHECK_CTX(ctx);
+    if (ctx->hp.pair.mode != PAIR_NONE) return fail(ctx, GC_ERR_STATE, "pair term already set");
+    if (!(sigma_a > 0) || !(sigma_b > 0)) return fail(ctx, GC_ERR_INVALID, "bad diameters");
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    ctx->hp.pair = {PAIR_AB, t, scale_by_core, 0, eps_a, sigma_a, eps_b, sigma_b};
+    return t;
+}
+
+int gc_add_pair_softcore(gc_ctx *ctx, double eps, double sigma)
+{
+    GC_CHECK_CTX(ctx);
+    if (ctx->hp.pair.mode != PAIR_NONE) return fail(ctx, GC_ERR_STATE, "pair term already set");
+    if (!(sigma > 0)) return fail(ctx, GC_ERR_INVALID, "bad diameter");
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    ctx->hp.pair = {PAIR_PLAIN, t, 0, 0, eps, sigma, 0.0, sigma};
+    return t;
+}
+
+int gc_add_pair_softwell(gc_ctx *ctx, double eps, double decay, double cutoff,
+                         int32_t n_targets, const int32_t *targets)
+{
+    GC_CHECK_CTX(ctx);
+    if (ctx->hp.well.term >= 0) return fail(ctx, GC_ERR_STATE, "droplet term already set");
+    if (n_targets < 0 || (n_targets && !targets)) return fail(ctx, GC_ERR_INVALID, "bad targets");
+    for (int k = 0; k < n_targets; k++) {
+        if (targets[k] < 0 || targets[k] >= ctx->n) return fail(ctx, GC_ERR_INVALID, "bad target");
+    }
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    ctx->well_targets.assign(targets, targets + n_targets);
+    ctx->hp.well.term = t;
+    ctx->hp.well.n_targets = n_targets;
+    ctx->hp.well.eps = eps;
+    ctx->hp.well.decay = decay;
+    ctx->hp.well.cutoff = cutoff;
+    ctx->topo_dirty = true;
+    return t;
+}
+
+int gc_add_bonds(gc_ctx *ctx, const gc_bond_params *params, int32_t n, const int32_t *pairs)
+{
+    GC_CHECK_CTX(ctx);
+    if (!params || n < 0 || (n && !pairs)) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (params->kind < 0 || params->kind > 2) return fail(ctx, GC_ERR_INVALID, "bad bond kind");
+    if (ctx->hp.n_bond_terms >= GC_MAX_BOND_TERMS) return fail(ctx, GC_ERR_INVALID, "too many bond terms");
+    for (int k = 0; k < 2 * n; k++) {
+        if (pairs[k] < 0 || pairs[k] >= ctx->n) return fail(ctx, GC_ERR_INVALID, "bond index out of range");
+    }
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    int b = ctx->hp.n_bond_terms++;
+    ctx->hp.bonds[b] = {params->kind, params->mix_ab, params->scale, t,
+                        params->K_a, params->K_b, params->l_a, params->l_b};
+    for (int k = 0; k < n; k++) ctx->bonds.push_back({pairs[2 * k], pairs[2 * k + 1], b});
+    ctx->topo_dirty = true;
+    return t;
+}
+
+int gc_add_triples(gc_ctx *ctx, double bending_energy, int32_t n, const int32_t *triples)
+{
+    GC_CHECK_CTX(ctx);
+    if (n < 0 || (n && !triples)) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (ctx->hp.n_triple_terms >= GC_MAX_TRIPLE_TERMS) return fail(ctx, GC_ERR_INVALID, "too many triple terms");
+    for (int k = 0; k < 3 * n; k++) {
+        if (triples[k] < 0 || triples[k] >= ctx->n) return fail(ctx, GC_ERR_INVALID, "triple index out of range");
+    }
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    int tt = ctx->hp.n_triple_terms++;
+    ctx->hp.triples[tt] = {t, 0, bending_energy};
+    for (int k = 0; k < n; k++) {
+        ctx->triples.push_back({triples[3 * k], triples[3 * k + 1], triples[3 * k + 2], tt});
+    }
+    ctx->topo_dirty = true;
+    return t;
+}
+
+int gc_set_wall(gc_ctx *ctx, const gc_wall_params *w)
+{
+    GC_CHECK_CTX(ctx);
+    if (!w) return fail(ctx, GC_ERR_INVALID, "null params");
+    if (ctx->hp.wall.term >= 0) return fail(ctx, GC_ERR_STATE, "wall already set");
+    for (int k = 0; k < 3; k++) {
+        if (!(w->semiaxes[k] > 0)) return fail(ctx, GC_ERR_INVALID, "bad semiaxes");
+    }
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    WallParams &W = ctx->hp.wall;
+    W.term = t;
+    W.scale_by_core = w->scale_by_core;
+    W.ode_enabled = w->ode_enabled;
+    W.eps_a = w->eps_a; W.sigma_a = w->sigma_a; W.eps_b = w->eps_b; W.sigma_b = w->sigma_b;
+    W.wall_a = w->wall_a; W.wall_b = w->wall_b;
+    W.outward_spring = w->outward_spring;
+    W.ode_mobility = w->ode_mobility;
+    for (int k = 0; k < 3; k++) W.ode_spring[k] = w->ode_spring[k];
+    int rc = modify_states(ctx, -1, [&](RepState &st, int) {
+        for (int k = 0; k < 3; k++) st.semiaxes[k] = w->semiaxes[k];
+    });
+    return rc ? rc : t;
+}
+
+int gc_add_point_source(gc_ctx *ctx, int32_t kind, const double point[3], double p0, double p1)
+{
+    GC_CHECK_CTX(ctx);
+    if (!point || kind < 0 || kind > 1) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (ctx->hp.n_sources >= GC_MAX_SOURCES) return fail(ctx, GC_ERR_INVALID, "too many sources");
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    SourceTerm &S = ctx->hp.sources[ctx->hp.n_sources++];
+    S.kind = kind;
+    S.term = t;
+    for (int k = 0; k < 3; k++) S.point[k] = point[k];
+    S.p0 = p0;
+    S.p1 = p1;
+    return t;
+}
+
+int gc_add_kfiber(gc_ctx *ctx, const double pole[3], int32_t n, const int32_t *beads,
+                  const double *spring, const double *length)
+{
+    GC_CHECK_CTX(ctx);
+    if (!pole || n < 0 || (n && (!beads || !spring || !length))) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (ctx->hp.n_poles >= GC_MAX_POLES) return fail(ctx, GC_ERR_INVALID, "too many poles");
+    for (int k = 0; k < n; k++) {
+        if (beads[k] < 0 || beads[k] >= ctx->n) return fail(ctx, GC_ERR_INVALID, "bead out of range");
+    }
+    int t = new_term(ctx);
+    if (t < 0) return t;
+    int p = ctx->hp.n_poles++;
+    for (int k = 0; k < 3; k++) ctx->hp.poles[p][k] = pole[k];
+    for (int k = 0; k < n; k++) {
+        ctx->tethers.push_back({beads[k], p, (float) spring[k], (float) length[k], t});
+    }
+    ctx->topo_dirty = true;
+    return t;
+}
+
+int gc_set_term_enabled(gc_ctx *ctx, int32_t term, int32_t enabled)
+{
+    GC_CHECK_CTX(ctx);
+    if (term < 0 || term >= ctx->next_term) return fail(ctx, GC_ERR_INVALID, "unknown term");
+    if (enabled) ctx->hp.enabled |= 1u << term;
+    else ctx->hp.enabled &= ~(1u << term);
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// schedule / context
+// ---------------------------------------------------------------------------
+
+int gc_set_schedule(gc_ctx *ctx, const gc_schedule *s)
+{
+    GC_CHECK_CTX(ctx);
+    if (!s) return fail(ctx, GC_ERR_INVALID, "null schedule");
+    ctx->hp.sched = {s->enabled, 0, s->core_init, s->core_tau, s->bond_init, s->bond_tau};
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+int gc_set_context(gc_ctx *ctx, int32_t replica, const gc_context *in)
+{
+    GC_CHECK_CTX(ctx);
+    if (!in) return fail(ctx, GC_ERR_INVALID, "null context");
+    return modify_states(ctx, replica, [&](RepState &st, int) {
+        st.time = in->time;
+        st.core_scale = in->core_scale;
+        st.bond_scale = in->bond_scale;
+        st.contact_distance = in->contact_distance;
+        st.contact_distance_prev = in->contact_distance;
+        for (int k = 0; k < 3; k++) st.semiaxes[k] = in->semiaxes[k];
+    });
+}
+
+int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    RepState st;
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    GC_CUDA(ctx, cudaMemcpy(&st, ctx->hp.st + replica, sizeof st, cudaMemcpyDeviceToHost));
+    out->time = st.time;
+    out->core_scale = st.core_scale;
+    out->bond_scale = st.bond_scale;
+    out->contact_distance = st.contact_distance;
+    out->reaction_force = st.reaction;
+    out->last_timestep = st.dt_last;
+    out->step = st.step;
+    out->rebuilds = st.rebuilds;
+    for (int k = 0; k < 3; k++) {
+        out->semiaxes[k] = st.semiaxes[k];
+        out->axial_reaction[k] = st.axial[k];
+    }
+    return GC_OK;
+}
+
+int gc_set_skin(gc_ctx *ctx, double skin_fraction)
+{
+    GC_CHECK_CTX(ctx);
+    if (!(skin_fraction >= 0.0)) return fail(ctx, GC_ERR_INVALID, "skin must be >= 0");
+    ctx->hp.skin = (float) skin_fraction;
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// launch plumbing
+// ---------------------------------------------------------------------------
+namespace {
+
+#define LAUNCH(ctx, kernel, grid, block, ...)                                                     do {                                                                                              kernel<<<grid, block, 0, (ctx)->stream>>>(__VA_ARGS__);                                       (ctx)->launches++;                                                                        } while (0)
+
+// Per-bead adjacency in CSR form + parameter upload.
+int finalize(gc_ctx *ctx)
+{
+    if (!ctx->attrs_set) return fail(ctx, GC_ERR_STATE, "gc_set_bead_attrs has not been called");
+    Params &P = ctx->hp;
+    const int n = ctx->n;
+    if (ctx->topo_dirty) {
+        std::vector<int> flags((size_t) n, 0);
+        std::vector<int> boff((size_t) n + 1, 0), toff((size_t) n + 1, 0), koff((size_t) n + 1, 0);
+        for (auto &b : ctx->bonds) { boff[b.i + 1]++; boff[b.j + 1]++; }
+        for (auto &t : ctx->triples) { toff[t.i + 1]++; toff[t.j + 1]++; toff[t.k + 1]++; }
+        for (auto &k : ctx->tethers) koff[k.bead + 1]++;
+        for (int i = 0; i < n; i++) {
+            boff[i + 1] += boff[i];
+            toff[i + 1] += toff[i];
+            koff[i + 1] += koff[i];
+        }
+        std::vector<BondEntry> bent((size_t) boff[n]);
+        std::vector<TripleEntry> tent((size_t) toff[n]);
+        std::vector<TetherEntry> kent((size_t) koff[n]);
+        {
+            std::vector<int> cur(boff.begin(), boff.end() - 1);
+            for (auto &b : ctx->bonds) {
+                bent[cur[b.i]++] = {b.j, b.bterm};
+                bent[cur[b.j]++] = {b.i, b.bterm};
+            }
+        }
+        {
+            std::vector<int> cur(toff.begin(), toff.end() - 1);
+            for (auto &t : ctx->triples) {
+                int members[3] = {t.i, t.j, t.k};
+                for (int role = 0; role < 3; role++) {
+                    tent[cur[members[role]]++] = {t.i, t.j, t.k, role | (t.tterm << 2)};
+                    flags[members[role]] |= 1;
+                }
+            }
+        }
+        {
+            std::vector<int> cur(koff.begin(), koff.end() - 1);
+            for (auto &k : ctx->tethers) {
+                kent[cur[k.bead]++] = {k.pole, k.spring, k.length, k.term};
+                flags[k.bead] |= 2;
+            }
+        }
+        for (int j : ctx->well_targets) flags[j] |= 4;
+
+        int rc = 0;
+        if (!rc) rc = upload(ctx, &ctx->d_flags, flags);
+        if (!rc) rc = upload(ctx, &ctx->d_bond_off, boff);
+        if (!rc) rc = upload(ctx, &ctx->d_triple_off, toff);
+        if (!rc) rc = upload(ctx, &ctx->d_tether_off, koff);
+        if (!rc) rc = upload(ctx, &ctx->d_bond_ent, bent);
+        if (!rc) rc = upload(ctx, &ctx->d_triple_ent, tent);
+        if (!rc) rc = upload(ctx, &ctx->d_tether_ent, kent);
+        if (!rc) rc = upload(ctx, &ctx->d_well_targets, ctx->well_targets);
+        if (rc) return rc;
+        P.flags = ctx->d_flags;
+        P.bond_off = ctx->d_bond_off;
+        P.bond_ent = ctx->d_bond_ent;
+        P.triple_off = ctx->d_triple_off;
+        P.triple_ent = ctx->d_triple_ent;
+        P.tether_off = ctx->d_tether_off;
+        P.tether_ent = ctx->d_tether_ent;
+        P.well.targets = ctx->d_well_targets;
+        ctx->topo_dirty = false;
+        ctx->params_dirty = true;
+    }
+    if (ctx->params_dirty) {
+        GC_CUDA(ctx, cudaMemcpyAsync(ctx->dp, &P, sizeof(Params), cudaMemcpyHostToDevice,
+                                     ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->params_dirty = false;
+        if (ctx->graph_exec) {   // parameters are read through dp, but be conservative
+            cudaGraphExecDestroy(ctx->graph_exec);
+            ctx->graph_exec = nullptr;
+        }
+    }
+    return GC_OK;
+}
+
+// bounding box + grid plan + forced rebuild of every replica's cell list
+int plan_and_rebuild(gc_ctx *ctx, double radius_override)
+{
+    const int R = ctx->n_rep;
+    LAUNCH(ctx, k_reset_reductions, (R + 63) / 64, 64, ctx->dp);
+    int bx = std::min((ctx->n + 255) / 256, 1024);
+    LAUNCH(ctx, k_bbox, dim3(std::max(bx, 1), R), 256, ctx->dp);
+    LAUNCH(ctx, k_plan, (R + 63) / 64, 64, ctx->dp, radius_override);
+    return GC_OK;
+}
+
+void launch_rebuild(gc_ctx *ctx)
+{
+    dim3 g = bead_grid(ctx, 256);
+    LAUNCH(ctx, k_count, g, 256, ctx->dp);
+    LAUNCH(ctx, k_scan, ctx->n_rep, SCAN_BS, ctx->dp);
+    LAUNCH(ctx, k_fill, g, 256, ctx->dp);
+    LAUNCH(ctx, k_gather, g, 256, ctx->dp);
+}
+
+int check_device_errors(gc_ctx *ctx)
+{
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    GC_CUDA(ctx, cudaGetLastError());
+    std::vector<RepState> st((size_t) ctx->n_rep);
+    GC_CUDA(ctx, cudaMemcpy(st.data(), ctx->hp.st, st.size() * sizeof(RepState),
+                            cudaMemcpyDeviceToHost));
+    for (int r = 0; r < ctx->n_rep; r++) {
+        if (st[r].error == 1) {
+            return fail(ctx, GC_ERR_NUMERIC, "replica %d: non-finite position or force at step %lld",
+                        r, st[r].step);
+        }
+        if (st[r].error == 2) {
+            return fail(ctx, GC_ERR_CAPACITY, "replica %d: contact table full (capacity %llu)", r,
+                        (unsigned long long) ctx->hp.contact.capacity);
+        }
+    }
+    return GC_OK;
+}
+
+__global__ void k_restart(Params *Pp, double dt)
+{
+    Params &P = *Pp;
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= P.n_rep) return;
+    RepState &st = P.st[r];
+    st.step = 0;
+    st.dt_last = dt;
+    st.dt_prev = dt;
+}
+
+} // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------------------
+// dynamics
+// ---------------------------------------------------------------------------
+
+int gc_run(gc_ctx *ctx, const gc_run_config *c)
+{
+    GC_CHECK_CTX(ctx);
+    if (!c || c->steps < 0 || !(c->timestep > 0) || !(c->temperature >= 0)) {
+        return fail(ctx, GC_ERR_INVALID, "bad run config");
+    }
+    if (c->noise && !c->restart) {
+        return fail(ctx, GC_ERR_INVALID, "injected noise requires restart = 1");
+    }
+    Params &P = ctx->hp;
+    const bool adaptive = c->spacestep != 0.0;
+    if (P.kT != (float) c->temperature || P.dt != (float) c->timestep ||
+        P.spacestep != (float) c->spacestep) {
+        P.kT = (float) c->temperature;
+        P.dt = (float) c->timestep;
+        P.spacestep = (float) c->spacestep;
+        ctx->params_dirty = true;
+    }
+
+    // injected noise: double [R][steps][N][3] -> float on device
+    const float *noise_dev = nullptr;
+    if (c->noise) {
+        size_t count = (size_t) ctx->n_rep * (size_t) c->steps * (size_t) ctx->n * 3;
+        if (count > ctx->noise_cap) {
+            if (ctx->d_noise) dev_free(ctx, ctx->d_noise);
+            ctx->d_noise = nullptr;
+            int rc = dev_alloc(ctx, &ctx->d_noise, count);
+            if (rc) return rc;
+            ctx->noise_cap = count;
+        }
+        std::vector<float> f(count);
+        for (size_t k = 0; k < count; k++) f[k] = (float) c->noise[k];
+        GC_CUDA(ctx, cudaMemcpyAsync(ctx->d_noise, f.data(), count * sizeof(float),
+                                     cudaMemcpyHostToDevice, ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        noise_dev = ctx->d_noise;
+    }
+    if (P.noise != noise_dev || P.noise_steps != c->steps) {
+        P.noise = noise_dev;
+        P.noise_steps = c->steps;
+        P.noise_step0 = 0;
+        ctx->params_dirty = true;
+    }
+
+    int rc = finalize(ctx);
+    if (rc) return rc;
+
+    if (c->restart) {
+        LAUNCH(ctx, k_restart, (ctx->n_rep + 63) / 64, 64, ctx->dp, c->timestep);
+        ctx->run_step = 0;
+    }
+    plan_and_rebuild(ctx, 0.0);
+
+    const long long interval = P.contact.enabled ? P.contact.interval : 0;
+    const dim3 g = bead_grid(ctx, BS);
+    for (long long i = 0; i < c->steps; i++) {
+        launch_rebuild(ctx);
+        // contact update of the driver callback for the step just finished
+        // (SIM/stage_interphase/simulation_driver_interphase.cpp:38-40)
+        if (interval > 0 && ctx->run_step > 0 && ctx->run_step % interval == 0 && i > 0) {
+            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, g, BS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+                   (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+        }
+        if (adaptive) {
+            LAUNCH(ctx, k_step<STEP_FORCE>, g, BS, ctx->dp, 0u, 1);
+            LAUNCH(ctx, k_integrate, g, BS, ctx->dp);
+        } else {
+            LAUNCH(ctx, k_step<STEP_FUSED>, g, BS, ctx->dp, 0u, 1);
+        }
+        ctx->run_step++;
+        ctx->parity ^= 1;
+    }
+    // the callback of the last step of this chunk
+    if (interval > 0 && c->steps > 0 && ctx->run_step % interval == 0) {
+        launch_rebuild(ctx);
+        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, g, BS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+               (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+    }
+    return check_device_errors(ctx);
+}
+
+int gc_debug_noise(gc_ctx *ctx, int32_t replica, int64_t step, float *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    float *d = nullptr;
+    rc = dev_alloc(ctx, &d, (size_t) ctx->n * 3);
+    if (rc) return rc;
+    LAUNCH(ctx, k_debug_noise, (ctx->n + 255) / 256, 256, ctx->dp, replica, (long long) step, d);
+    GC_CUDA(ctx, cudaMemcpyAsync(out, d, (size_t) ctx->n * 3 * sizeof(float),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    dev_free(ctx, d);
+    return GC_OK;
+}
+
+int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    plan_and_rebuild(ctx, 0.0);
+    launch_rebuild(ctx);
+    LAUNCH(ctx, k_step<STEP_FORCE>, bead_grid(ctx, BS), BS, ctx->dp, term_mask, 0);
+    std::vector<float4> f((size_t) ctx->n);
+    GC_CUDA(ctx, cudaMemcpyAsync(f.data(), ctx->hp.force + (size_t) replica * ctx->n,
+                                 f.size() * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    rc = check_device_errors(ctx);
+    if (rc) return rc;
+    for (int i = 0; i < ctx->n; i++) {
+        out[3 * i] = f[i].x;
+        out[3 * i + 1] = f[i].y;
+        out[3 * i + 2] = f[i].z;
+    }
+    return GC_OK;
+}
+
+int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    plan_and_rebuild(ctx, 0.0);
+    launch_rebuild(ctx);
+    int nb = (ctx->n + BS - 1) / BS;
+    LAUNCH(ctx, k_energy, std::max(nb, 1), BS, ctx->dp, replica, term_mask, ctx->d_partials);
+    std::vector<double> part((size_t) std::max(nb, 1));
+    GC_CUDA(ctx, cudaMemcpyAsync(part.data(), ctx->d_partials, part.size() * sizeof(double),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    rc = check_device_errors(ctx);
+    if (rc) return rc;
+    double e = 0;
+    for (int b = 0; b < nb; b++) e += part[b];
+    *out = e;
+    return GC_OK;
+}
+
+int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pairs,
+                      size_t capacity, size_t *count)
+{
+    GC_CHECK_CTX(ctx);
+    if (!count || replica < 0 || replica >= ctx->n_rep || !(radius > 0)) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    plan_and_rebuild(ctx, radius);
+    launch_rebuild(ctx);
+    uint2 *d_out = nullptr;
+    rc = dev_alloc(ctx, &d_out, capacity);
+    if (rc) return rc;
+    GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
+    LAUNCH(ctx, k_pairs<PAIRS_LIST>, bead_grid(ctx, BS), BS, ctx->dp, radius, (int) RADIUS_ARG,
+           replica, d_out, (unsigned long long) capacity, ctx->d_counter);
+    unsigned long long found = 0;
+    GC_CUDA(ctx, cudaMemcpyAsync(&found, ctx->d_counter, sizeof found, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    rc = check_device_errors(ctx);
+    if (rc) { dev_free(ctx, d_out); return rc; }
+    *count = (size_t) found;
+    size_t m = std::min<size_t>(found, capacity);
+    std::vector<uint2> host(m);
+    if (m && pairs) {
+        GC_CUDA(ctx, cudaMemcpy(host.data(), d_out, m * sizeof(uint2), cudaMemcpyDeviceToHost));
+        std::sort(host.begin(), host.end(), [](uint2 a, uint2 b) {
+            return a.x != b.x ? a.x < b.x : a.y < b.y;
+        });
+        for (size_t k = 0; k < m; k++) {
+            pairs[2 * k] = host[k].x;
+            pairs[2 * k + 1] = host[k].y;
+        }
+    }
+    dev_free(ctx, d_out);
+    if (found > capacity) return fail(ctx, GC_ERR_CAPACITY, "pair buffer too small: %llu pairs", found);
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// contact map
+// ---------------------------------------------------------------------------
+
+int gc_set_contact_map(gc_ctx *ctx, double distance, int64_t interval, int32_t scale_by_core,
+                       size_t table_capacity)
+{
+    GC_CHECK_CTX(ctx);
+    if (!(distance >= 0) || interval < 0) return fail(ctx, GC_ERR_INVALID, "bad args");
+    ContactParams &C = ctx->hp.contact;
+    size_t cap = table_capacity ? table_capacity : std::max<size_t>(64 * (size_t) ctx->n, 1 << 16);
+    size_t pow2 = 1;
+    while (pow2 < cap) pow2 <<= 1;
+    if (!C.keys || C.capacity != pow2) {
+        if (C.keys) dev_free(ctx, C.keys);
+        if (C.vals) dev_free(ctx, C.vals);
+        if (C.used) dev_free(ctx, C.used);
+        C.keys = nullptr; C.vals = nullptr; C.used = nullptr;
+        int rc = dev_alloc(ctx, &C.keys, pow2 * ctx->n_rep, 0xff);
+        if (!rc) rc = dev_alloc(ctx, &C.vals, pow2 * ctx->n_rep);
+        if (!rc) rc = dev_alloc(ctx, &C.used, (size_t) ctx->n_rep);
+        if (rc) return rc;
+        C.capacity = pow2;
+    }
+    C.base_distance = distance;
+    C.interval = interval;
+    C.scale_by_core = scale_by_core;
+    C.enabled = distance > 0;
+    ctx->params_dirty = true;
+    // contact distance in force now (SIM/stage_interphase/simulation_driver_interphase.cpp:75)
+    return modify_states(ctx, -1, [&](RepState &st, int) {
+        st.contact_distance = scale_by_core ? distance * st.core_scale : distance;
+        st.contact_distance_prev = st.contact_distance;
+    });
+}
+
+int gc_contacts_update(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    if (!ctx->hp.contact.enabled) return fail(ctx, GC_ERR_STATE, "contact map is not configured");
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    plan_and_rebuild(ctx, 0.0);
+    launch_rebuild(ctx);
+    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, BS), BS, ctx->dp, 0.0, (int) RADIUS_CONTACT,
+           -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+    return check_device_errors(ctx);
+}
+
+int gc_contacts_clear(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    ContactParams &C = ctx->hp.contact;
+    if (!C.keys) return GC_OK;
+    GC_CUDA(ctx, cudaMemsetAsync(C.keys, 0xff, C.capacity * ctx->n_rep * sizeof(unsigned long long),
+                                 ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(C.vals, 0, C.capacity * ctx->n_rep * sizeof(unsigned int),
+                                 ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(C.used, 0, ctx->n_rep * sizeof(unsigned int), ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
+}
+
+int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity, size_t *count)
+{
+    GC_CHECK_CTX(ctx);
+    if (!count || replica < -1 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    ContactParams &C = ctx->hp.contact;
+    *count = 0;
+    if (!C.keys) return GC_OK;
+    int rc = finalize(ctx);
+    if (rc) return rc;
+
+    std::vector<unsigned int> used((size_t) ctx->n_rep);
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    GC_CUDA(ctx, cudaMemcpy(used.data(), C.used, used.size() * sizeof(unsigned int),
+                            cudaMemcpyDeviceToHost));
+    size_t m = 0;
+    for (int r = 0; r < ctx->n_rep; r++) {
+        if (replica < 0 || r == replica) m += used[r];
+    }
+    if (m == 0) return GC_OK;
+
+    unsigned long long *k_in = nullptr, *k_out = nullptr, *k_red = nullptr, *d_runs = nullptr;
+    unsigned int *v_in = nullptr, *v_out = nullptr, *v_red = nullptr;
+    void *tmp = nullptr;
+    auto cleanup = [&] {
+        dev_free(ctx, k_in); dev_free(ctx, k_out); dev_free(ctx, k_red); dev_free(ctx, d_runs);
+        dev_free(ctx, v_in); dev_free(ctx, v_out); dev_free(ctx, v_red);
+        if (tmp) dev_free(ctx, tmp);
+    };
+    rc = dev_alloc(ctx, &k_in, m);
+    if (!rc) rc = dev_alloc(ctx, &k_out, m);
+    if (!rc) rc = dev_alloc(ctx, &v_in, m);
+    if (!rc) rc = dev_alloc(ctx, &v_out, m);
+    if (!rc) rc = dev_alloc(ctx, &d_runs, 1);
+    if (rc) { cleanup(); return rc; }
+
+    GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
+    LAUNCH(ctx, k_contact_compact, 148 * 8, 256, ctx->dp, replica, k_in, v_in, ctx->d_counter);
+
+    // sort by key = (i << 32 | j): the order contact_map::accumulate produces
+    // (SIM/stage_interphase/contact_map.cpp:75-82)
+    size_t tmp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
+                                    ctx->stream);
+    size_t tmp2 = 0;
+    if (replica < 0) {
+        cub::DeviceReduce::ReduceByKey(nullptr, tmp2, k_out, k_in, v_out, v_in, d_runs,
+                                       cub::Sum(), (int) m, ctx->stream);
+    }
+    tmp_bytes = std::max(tmp_bytes, tmp2);
+    {
+        unsigned char *t8 = nullptr;
+        rc = dev_alloc(ctx, &t8, tmp_bytes);
+        if (rc) { cleanup(); return rc; }
+        tmp = t8;
+    }
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
+                                    ctx->stream);
+    ctx->launches += 8;
+    size_t n_out = m;
+    const unsigned long long *k_res = k_out;
+    const unsigned int *v_res = v_out;
+    if (replica < 0) {
+        // ensemble sum: equal keys of different replicas are adjacent after the sort
+        cub::DeviceReduce::ReduceByKey(tmp, tmp_bytes, k_out, k_in, v_out, v_in, d_runs, cub::Sum(),
+                                       (int) m, ctx->stream);
+        ctx->launches += 2;
+        unsigned long long runs = 0;
+        GC_CUDA(ctx, cudaMemcpyAsync(&runs, d_runs, sizeof runs, cudaMemcpyDeviceToHost, ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        n_out = (size_t) runs;
+        k_res = k_in;
+        v_res = v_in;
+    }
+    *count = n_out;
+    if (ijv) {
+        size_t take = std::min(n_out, capacity);
+        std::vector<unsigned long long> hk(take);
+        std::vector<unsigned int> hv(take);
+        GC_CUDA(ctx, cudaMemcpyAsync(hk.data(), k_res, take * sizeof(unsigned long long),
+                                     cudaMemcpyDeviceToHost, ctx->stream));
+        GC_CUDA(ctx, cudaMemcpyAsync(hv.data(), v_res, take * sizeof(unsigned int),
+                                     cudaMemcpyDeviceToHost, ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        for (size_t k = 0; k < take; k++) {
+            ijv[3 * k] = (uint32_t) (hk[k] >> 32);
+            ijv[3 * k + 1] = (uint32_t) hk[k];
+            ijv[3 * k + 2] = hv[k];
+        }
+    }
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cleanup();
+    if (ijv && n_out > capacity) return fail(ctx, GC_ERR_CAPACITY, "contact buffer too small: %zu", n_out);
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// observables, misc
+// ---------------------------------------------------------------------------
+
+int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges, const int32_t *ranges,
+                          double *out_rg2)
+{
+    GC_CHECK_CTX(ctx);
+    if (replica < 0 || replica >= ctx->n_rep || n_ranges < 0 || (n_ranges && (!ranges || !out_rg2))) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    if (n_ranges == 0) return GC_OK;
+    for (int g = 0; g < n_ranges; g++) {
+        if (ranges[2 * g] < 0 || ranges[2 * g + 1] > ctx->n || ranges[2 * g] > ranges[2 * g + 1]) {
+            return fail(ctx, GC_ERR_INVALID, "bad range %d", g);
+        }
+    }
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    int *d_ranges = nullptr;
+    double *d_out = nullptr;
+    rc = dev_alloc(ctx, &d_ranges, (size_t) 2 * n_ranges);
+    if (!rc) rc = dev_alloc(ctx, &d_out, (size_t) n_ranges);
+    if (rc) return rc;
+    GC_CUDA(ctx, cudaMemcpyAsync(d_ranges, ranges, (size_t) 2 * n_ranges * sizeof(int),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_rg2, n_ranges, 256, ctx->dp, replica, n_ranges, d_ranges, d_out);
+    GC_CUDA(ctx, cudaMemcpyAsync(out_rg2, d_out, (size_t) n_ranges * sizeof(double),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    dev_free(ctx, d_ranges);
+    dev_free(ctx, d_out);
+    return GC_OK;
+}
+
+int gc_launch_count(gc_ctx *ctx, int64_t *out)
+{
+    if (!ctx || !out) return GC_ERR_INVALID;
+    *out = ctx->launches;
+    return GC_OK;
+}
+
+int gc_synchronize(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    return check_device_errors(ctx);
+}
+
+int gc_stream(gc_ctx *ctx, void **out)
+{
+    if (!ctx || !out) return GC_ERR_INVALID;
+    *out = (void *) ctx->stream;
+    return GC_OK;
+}
+
+} // extern "C"

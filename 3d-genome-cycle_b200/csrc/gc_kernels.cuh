@@ -1,0 +1,281 @@
+// gc_kernels.cuh -- sm_100a kernels of the hot path (part 1: helpers, cell
+// list construction).  One thread block grid is (ceil(N / BS), R): blockIdx.y
+// selects the replica.
+//
+// Neighbor search replaces md::neighbor_searcher<open_box> + md::neighbor_list
+// (MD/misc/neighbor_searcher.hpp:22-131, MD/forcefield/detail/neighbor_list.hpp:
+// 62-240): instead of a hashed grid + stored Verlet pair list on the host, beads
+// are counting-sorted into a dense x-fastest cell grid in HBM and every step
+// walks the (2M+1)^2 contiguous x-rows of neighbouring cells directly (no pair
+// list is ever stored).  The pair SET that results is identical (tests).
+#pragma once
+
+#include "gc_math.cuh"
+#include "gc_types.cuh"
+
+namespace gc {
+
+constexpr int BS = 128;          // threads per block of the per-bead kernels
+constexpr int SCAN_BS = 1024;
+
+// ---------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------
+
+__device__ __forceinline__ double pair_cutoff(const Params &P, const RepState &st)
+{
+    if (P.pair.mode == PAIR_NONE) return 0.0;
+    double s = P.pair.scale_by_core ? st.core_scale : 1.0;
+    if (P.pair.mode == PAIR_PLAIN) return P.pair.sigma_a * s;
+    return fmax(P.pair.sigma_a, P.pair.sigma_b) * s;
+}
+
+// Radius the cell list has to resolve for this replica right now.
+__device__ __forceinline__ double interaction_radius(const Params &P, const RepState &st)
+{
+    double r = pair_cutoff(P, st);
+    if (P.contact.enabled) {
+        r = fmax(r, fmax(st.contact_distance, st.contact_distance_prev));
+    }
+    return r;
+}
+
+__device__ __forceinline__ PairCoef make_pair_coef(double eps_a, double sigma_a, double eps_b,
+                                                   double sigma_b, double s, int mode)
+{
+    PairCoef c;
+    double dA = sigma_a * s, dB = sigma_b * s;
+    double kA2 = 1.0 / (dA * dA);
+    double kB2 = mode == PAIR_PLAIN ? 0.0 : 1.0 / (dB * dB);
+    c.kA2 = (float) kA2;
+    c.kB2 = (float) kB2;
+    c.cA = (float) (6.0 * eps_a * kA2);
+    c.cB = (float) (24.0 * eps_b * kB2);
+    c.eA = (float) eps_a;
+    c.eB = mode == PAIR_PLAIN ? 0.0f : (float) eps_b;
+    double rc = mode == PAIR_PLAIN ? dA : fmax(dA, dB);
+    c.rc2 = (float) (rc * rc);
+    return c;
+}
+
+__device__ __forceinline__ int cell_coord(float x, float origin, float inv, int dim)
+{
+    int c = (int) floorf((x - origin) * inv);
+    return min(max(c, 0), dim - 1);
+}
+
+__device__ __forceinline__ int cell_index(const RepState &st, float4 p)
+{
+    int cx = cell_coord(p.x, st.origin[0], st.inv_cell, st.dims[0]);
+    int cy = cell_coord(p.y, st.origin[1], st.inv_cell, st.dims[1]);
+    int cz = cell_coord(p.z, st.origin[2], st.inv_cell, st.dims[2]);
+    return cx + st.dims[0] * (cy + st.dims[1] * cz);
+}
+
+// Chooses origin / cell size / dims from the bounding box for list radius
+// `rlist`.  Cells outside the box are folded into the boundary cells by
+// clamping, which never separates two beads further than their true cell
+// distance, so no pair within rlist can be missed.
+__device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
+{
+    float lo[3], hi[3];
+    for (int k = 0; k < 3; k++) {
+        lo[k] = ordered_to_float(st.bbox_min[k]);
+        hi[k] = ordered_to_float(st.bbox_max[k]);
+        if (!(hi[k] >= lo[k]) || isinf(lo[k]) || isinf(hi[k])) {   // NaN/Inf or empty
+            if (P.n > 0) st.error = 1;
+            lo[k] = 0.0f;
+            hi[k] = 0.0f;
+        }
+    }
+    if (!(rlist > 0.0)) rlist = 1.0;
+    double cs = rlist / P.cells_per_cut;
+    int dims[3];
+    for (;;) {
+        double tot = 1.0;
+        for (int k = 0; k < 3; k++) {
+            double e = (double) hi[k] - (double) lo[k];
+            double d = floor(e / cs) + 1.0;
+            if (d > 1.0e6) d = 1.0e6;
+            dims[k] = (int) d;
+            tot *= d;
+        }
+        if (tot <= (double) P.ncell_max) break;
+        cs *= 1.2599210498948732;   // 2^(1/3): halves the cell count per round
+    }
+    for (int k = 0; k < 3; k++) {
+        st.dims[k] = dims[k];
+        st.origin[k] = lo[k];
+    }
+    st.ncell = dims[0] * dims[1] * dims[2];
+    st.cell_size = (float) cs;
+    st.inv_cell = (float) (1.0 / cs);
+    // A pair is guaranteed to be seen while (distance now) + 2 max displacement
+    // <= M * cell edge.  The float cell edge may round below cs, so keep a
+    // hair of margin.
+    st.rc_valid = (float) (cs * P.cells_per_cut * (1.0 - 1.0e-6));
+}
+
+// ---------------------------------------------------------------------------
+// bounding box + grid planning (run start, explicit force / pair queries)
+// ---------------------------------------------------------------------------
+
+__global__ void k_reset_reductions(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= P.n_rep) return;
+    RepState &st = P.st[r];
+    for (int k = 0; k < 3; k++) {
+        st.bbox_min[k] = 0x7fffffff;
+        st.bbox_max[k] = (int) 0x80000000;
+        st.axial_fx[k] = 0;
+    }
+    st.reaction_fx = 0;
+    st.maxdisp2_bits = 0u;
+    st.dtmin_bits = 0x7f800000u;
+    st.ticket = 0u;
+}
+
+__global__ void k_bbox(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.y;
+    RepState &st = P.st[r];
+    const float4 *pos = P.pos[st.parity] + (size_t) r * P.n;
+    float lo[3] = {INFINITY, INFINITY, INFINITY};
+    float hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    bool bad = false;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n; i += gridDim.x * blockDim.x) {
+        float4 p = pos[i];
+        float v[3] = {p.x, p.y, p.z};
+        for (int k = 0; k < 3; k++) {
+            lo[k] = fminf(lo[k], v[k]);
+            hi[k] = fmaxf(hi[k], v[k]);
+            bad |= !(fabsf(v[k]) < INFINITY);
+        }
+    }
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0) {
+        for (int k = 0; k < 3; k++) {
+            atomicMin(&st.bbox_min[k], float_to_ordered(lo[k]));
+            atomicMax(&st.bbox_max[k], float_to_ordered(hi[k]));
+        }
+        if (bad) st.error = 1;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// cell list construction: count -> scan -> fill -> gather (deterministic:
+// beads inside a cell end up ordered by original index)
+// ---------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256) k_count(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.y;
+    const RepState &st = P.st[r];
+    if (!st.need_rebuild) return;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    float4 p = P.pos[st.parity][(size_t) r * P.n + i];
+    int c = cell_index(st, p);
+    P.cell_of[(size_t) r * P.n + i] = c;
+    atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
+}
+
+__global__ void __launch_bounds__(SCAN_BS) k_scan(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.x;
+    const RepState &st = P.st[r];
+    if (!st.need_rebuild) return;
+    int *count = P.cell_count + (size_t) r * P.ncell_max;
+    int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    int ncell = st.ncell;
+
+    __shared__ int warp_sums[SCAN_BS / 32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int base = 0; base < ncell; base += SCAN_BS) {
+        int c = base + threadIdx.x;
+        int v = c < ncell ? count[c] : 0;
+        if (c < ncell) count[c] = 0;           // ready for k_fill's cursor
+        int x = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sums[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int w = warp_sums[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            warp_sums[lane] = w;               // inclusive over warps
+        }
+        __syncthreads();
+        int warp_off = wid == 0 ? 0 : warp_sums[wid - 1];
+        int excl = carry + warp_off + x - v;
+        if (c < ncell) start[c] = excl;
+        __syncthreads();
+        if (threadIdx.x == SCAN_BS - 1) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) start[ncell] = carry;
+}
+
+__global__ void __launch_bounds__(256) k_fill(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.y;
+    const RepState &st = P.st[r];
+    if (!st.need_rebuild) return;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    int c = P.cell_of[(size_t) r * P.n + i];
+    int s = P.cell_start[(size_t) r * (P.ncell_max + 1) + c] +
+            atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
+    P.members[(size_t) r * P.n + s] = i;
+}
+
+__global__ void __launch_bounds__(256) k_gather(Params *Pp)
+{
+    Params &P = *Pp;
+    int r = blockIdx.y;
+    const RepState &st = P.st[r];
+    if (!st.need_rebuild) return;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.n) return;
+    size_t ro = (size_t) r * P.n;
+    const int *members = P.members + ro;
+    int idx = members[s];
+    int c = P.cell_of[ro + idx];
+    const int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    int base = start[c], end = start[c + 1];
+    int rank = 0;
+    for (int k = base; k < end; k++) rank += members[k] < idx;
+    if (rank == 0) P.cell_count[(size_t) r * P.ncell_max + c] = 0;   // cursor back to 0
+    int dst = base + rank;
+    float4 p = P.pos[st.parity][ro + idx];
+    p.w = __int_as_float(idx);
+    P.spos[st.parity][ro + dst] = p;
+    P.sref[ro + dst] = p;
+    P.sidx[ro + dst] = idx;
+    P.scell[ro + dst] = c;
+    P.slot_of[ro + idx] = dst;
+    P.sab[ro + dst] = P.ab[idx];
+}
+
+} // namespace gc

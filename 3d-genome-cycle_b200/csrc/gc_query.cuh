@@ -1,0 +1,309 @@
+// gc_query.cuh -- pair enumeration (neighbor search output, contact map),
+// potential energy, observables.  Same cell walk as the force kernel.
+#pragma once
+
+#include "gc_step.cuh"
+
+namespace gc {
+
+#define GC_EMPTY_KEY 0xffffffffffffffffull
+
+__device__ __forceinline__ unsigned long long hash64(unsigned long long k)
+{
+    // splitmix64 finaliser
+    k ^= k >> 30; k *= 0xbf58476d1ce4e5b9ull;
+    k ^= k >> 27; k *= 0x94d049bb133111ebull;
+    k ^= k >> 31;
+    return k;
+}
+
+// contact_map::update's `contacts[{i, j}] += 1`
+// (SIM/stage_interphase/contact_map.cpp:52-58) on an open-addressing table.
+__device__ __forceinline__ void contact_insert(const ContactParams &C, int r, RepState &st,
+                                               unsigned int i, unsigned int j)
+{
+    unsigned long long key = ((unsigned long long) i << 32) | j;
+    unsigned long long mask = C.capacity - 1;
+    unsigned long long *keys = C.keys + (size_t) r * C.capacity;
+    unsigned int *vals = C.vals + (size_t) r * C.capacity;
+    unsigned long long h = hash64(key) & mask;
+    for (unsigned long long probe = 0; probe < C.capacity; probe++) {
+        unsigned long long cur = keys[h];
+        if (cur == GC_EMPTY_KEY) {
+            cur = atomicCAS(&keys[h], GC_EMPTY_KEY, key);
+            if (cur == GC_EMPTY_KEY) {
+                atomicAdd(&C.used[r], 1u);
+                cur = key;
+            }
+        }
+        if (cur == key) {
+            atomicAdd(&vals[h], 1u);
+            return;
+        }
+        h = (h + 1) & mask;
+    }
+    atomicExch(&st.error, 2);   // table full
+}
+
+enum PairsMode : int { PAIRS_LIST = 0, PAIRS_CONTACT = 1 };
+enum RadiusSel : int { RADIUS_ARG = 0, RADIUS_CONTACT = 1, RADIUS_CONTACT_PREV = 2 };
+
+// Emits every unordered pair (i < j, original indices) with |xi - xj|^2 <= rc^2
+// exactly once -- the contract of md::neighbor_searcher::search
+// (MD/misc/neighbor_searcher.hpp:75-100, inclusive test at line 90).  The FP32
+// distance decides except inside a 1e-4 relative band around rc^2, where the
+// test is redone in FP64 on the (exactly representable) FP32 coordinates, so
+// the set equals the FP64 reference's on the same inputs.
+template<int MODE>
+__global__ void __launch_bounds__(BS) k_pairs(Params *Pp, double rc_arg, int radius_sel,
+                                              int replica, uint2 *out,
+                                              unsigned long long out_cap,
+                                              unsigned long long *out_count)
+{
+    Params &P = *Pp;
+    const int r = blockIdx.y;
+    RepState &st = P.st[r];
+    if (replica >= 0 && r != replica) return;
+    const int t = blockIdx.x * BS + threadIdx.x;
+    if (t >= P.n) return;
+    double rc = radius_sel == RADIUS_ARG ? rc_arg
+              : radius_sel == RADIUS_CONTACT ? st.contact_distance : st.contact_distance_prev;
+    if (!(rc > 0.0)) return;
+    const double rc2d = rc * rc;
+    const float rc2 = (float) rc2d;
+    const float band = 1.0e-4f * rc2;
+
+    const size_t ro = (size_t) r * P.n;
+    const float4 *__restrict__ sp = P.spos[st.parity] + ro;
+    const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    const float4 self = sp[t];
+    const int idx = __float_as_int(self.w);
+    const int dx = st.dims[0], dy = st.dims[1], dz = st.dims[2];
+    const int M = P.cells_per_cut;
+    int c = P.scell[ro + t];
+    int cx = c % dx, cy = (c / dx) % dy, cz = c / (dx * dy);
+    int x0 = max(cx - M, 0), x1 = min(cx + M, dx - 1);
+    for (int z = max(cz - M, 0); z <= min(cz + M, dz - 1); z++) {
+        for (int y = max(cy - M, 0); y <= min(cy + M, dy - 1); y++) {
+            int row = dx * (y + dy * z);
+            int lo = start[row + x0], hi = start[row + x1 + 1];
+            for (int j = lo; j < hi; j++) {
+                float4 q = __ldg(&sp[j]);
+                int jdx = __float_as_int(q.w);
+                if (jdx <= idx) continue;
+                float ex = self.x - q.x, ey = self.y - q.y, ez = self.z - q.z;
+                float r2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+                bool in = r2 <= rc2;
+                if (fabsf(r2 - rc2) <= band) {
+                    double fx = (double) self.x - (double) q.x;
+                    double fy = (double) self.y - (double) q.y;
+                    double fz = (double) self.z - (double) q.z;
+                    in = fx * fx + fy * fy + fz * fz <= rc2d;
+                }
+                if (!in) continue;
+                if (MODE == PAIRS_CONTACT) {
+                    contact_insert(P.contact, r, st, (unsigned) idx, (unsigned) jdx);
+                } else {
+                    unsigned long long k = atomicAdd(out_count, 1ull);
+                    if (k < out_cap) out[k] = make_uint2((unsigned) idx, (unsigned) jdx);
+                }
+            }
+        }
+    }
+}
+
+// Compacts the non-empty slots of one replica's table (replica >= 0) or of
+// all replicas (replica < 0) into (key, count) arrays.
+__global__ void k_contact_compact(Params *Pp, int replica, unsigned long long *out_keys,
+                                  unsigned int *out_vals, unsigned long long *out_count)
+{
+    const ContactParams &C = Pp->contact;
+    unsigned long long total = (replica < 0 ? (unsigned long long) Pp->n_rep : 1ull) * C.capacity;
+    unsigned long long base = replica < 0 ? 0ull : (unsigned long long) replica * C.capacity;
+    for (unsigned long long s = blockIdx.x * (unsigned long long) blockDim.x + threadIdx.x;
+         s < total; s += (unsigned long long) gridDim.x * blockDim.x) {
+        unsigned long long k = C.keys[base + s];
+        if (k == GC_EMPTY_KEY) continue;
+        unsigned long long o = atomicAdd(out_count, 1ull);
+        out_keys[o] = k;
+        out_vals[o] = C.vals[base + s];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// potential energy (md::system::compute_potential_energy, MD/system.hpp:249-252)
+// every interaction is counted by exactly one thread; per-block partial sums
+// in FP64 are added on the host in block order (deterministic).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(BS) k_energy(Params *Pp, int r, unsigned mask_arg,
+                                               double *partials)
+{
+    Params &P = *Pp;
+    RepState &st = P.st[r];
+    const StepConst &sc = st.sc;
+    const unsigned mask = mask_arg & P.enabled;
+    const int t = blockIdx.x * BS + threadIdx.x;
+    double E = 0.0;
+
+    if (t < P.n) {
+        const size_t ro = (size_t) r * P.n;
+        const int par = st.parity;
+        const float4 *__restrict__ sp = P.spos[par] + ro;
+        const float4 *__restrict__ pos = P.pos[par] + ro;
+        const float4 self4 = sp[t];
+        const f3 self = make_f3(self4);
+        const int idx = __float_as_int(self4.w);
+        const float2 abi = P.sab[ro + t];
+        const int flags = P.flags[idx];
+
+        if (P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u)) {
+            PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
+            const bool plain = P.pair.mode == PAIR_PLAIN;
+            const float2 *__restrict__ sab = P.sab + ro;
+            const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+            const int dx = st.dims[0], dy = st.dims[1], dz = st.dims[2];
+            const int M = P.cells_per_cut;
+            int c = P.scell[ro + t];
+            int cx = c % dx, cy = (c / dx) % dy, cz = c / (dx * dy);
+            int x0 = max(cx - M, 0), x1 = min(cx + M, dx - 1);
+            for (int z = max(cz - M, 0); z <= min(cz + M, dz - 1); z++) {
+                for (int y = max(cy - M, 0); y <= min(cy + M, dy - 1); y++) {
+                    int row = dx * (y + dy * z);
+                    int lo = max(start[row + x0], t + 1), hi = start[row + x1 + 1];
+                    for (int j = lo; j < hi; j++) {   // slots above t only: each pair once
+                        float4 q = __ldg(&sp[j]);
+                        f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
+                        float r2 = dot(d, d);
+                        if (r2 < pc.rc2) {
+                            float a = 1.0f, b = 0.0f;
+                            if (!plain) {
+                                float2 abj = __ldg(&sab[j]);
+                                a = 0.5f * (abi.x + abj.x);
+                                b = 0.5f * (abi.y + abj.y);
+                            }
+                            E += (double) pair_energy(pc, a, b, r2);
+                        }
+                    }
+                }
+            }
+        }
+        for (int e = P.bond_off[idx]; e < P.bond_off[idx + 1]; e++) {
+            BondEntry be = P.bond_ent[e];
+            const BondTerm &bt = P.bonds[be.bterm];
+            if (!(mask >> bt.term & 1u) || be.partner < idx) continue;
+            if (be.partner == idx) continue;
+            f3 d = self - make_f3(pos[be.partner]);
+            float K = sc.bK_a[be.bterm], l = sc.bl_a[be.bterm];
+            if (bt.mix_ab) {
+                float2 abj = P.ab[be.partner];
+                float a = 0.5f * (abi.x + abj.x), b = 0.5f * (abi.y + abj.y);
+                K = a * sc.bK_a[be.bterm] + b * sc.bK_b[be.bterm];
+                l = a * sc.bl_a[be.bterm] + b * sc.bl_b[be.bterm];
+            }
+            E += (double) bond_energy(bt.kind, K, l, dot(d, d));
+        }
+        if (flags & 1) {
+            for (int e = P.triple_off[idx]; e < P.triple_off[idx + 1]; e++) {
+                TripleEntry te = P.triple_ent[e];
+                int tt = te.role_term >> 2, role = te.role_term & 3;
+                if (role != 1 || !(mask >> P.triples[tt].term & 1u)) continue;
+                f3 pi = make_f3(pos[te.i]), pj = make_f3(pos[te.j]), pk = make_f3(pos[te.k]);
+                E += (double) bending_energy(sc.tE[tt], pi - pj, pj - pk);
+            }
+        }
+        if (flags & 2) {
+            for (int e = P.tether_off[idx]; e < P.tether_off[idx + 1]; e++) {
+                TetherEntry te = P.tether_ent[e];
+                if (!(mask >> te.term & 1u)) continue;
+                f3 d = {self.x - sc.pole[te.pole][0], self.y - sc.pole[te.pole][1],
+                        self.z - sc.pole[te.pole][2]};
+                E += (double) bond_energy(2, te.spring, te.length, dot(d, d));
+            }
+        }
+        if ((flags & 4) && P.well.term >= 0 && (mask >> P.well.term & 1u)) {
+            for (int k = 0; k < P.well.n_targets; k++) {
+                int j = P.well.targets[k];
+                if (j <= idx) continue;
+                f3 d = self - make_f3(pos[j]);
+                E += (double) well_energy(sc.well_eps, sc.well_k2, sc.well_cut2, dot(d, d));
+            }
+        }
+        for (int k = 0; k < P.n_sources; k++) {
+            if (!(mask >> P.sources[k].term & 1u)) continue;
+            f3 d = {self.x - sc.src_pt[k][0], self.y - sc.src_pt[k][1], self.z - sc.src_pt[k][2]};
+            float r2 = dot(d, d);
+            E += (double) (P.sources[k].kind == 0 ? bond_energy(0, sc.src_p0[k], sc.src_p1[k], r2)
+                                                  : flux_energy(sc.src_p0[k], sc.src_p1[k], r2));
+        }
+        if (P.wall.term >= 0 && (mask >> P.wall.term & 1u)) {
+            f3 dual = {sc.q[0] * self.x, sc.q[1] * self.y, sc.q[2] * self.z};
+            float dd = dot(dual, dual);
+            if (dd != 0.0f) {
+                float phi = fmaf(dual.x, self.x, fmaf(dual.y, self.y, fmaf(dual.z, self.z, -1.0f)));
+                float kappa = phi / (2.0f * dd);
+                f3 delta = kappa * dual;
+                float d2 = dot(delta, delta);
+                if (phi < 0.0f) {
+                    PairCoef wc = {sc.w_kA2, sc.w_kB2, sc.w_cA, sc.w_cB, sc.w_eA, sc.w_eB, 0.0f};
+                    float a = 0.5f * (abi.x + sc.wall_a), b = 0.5f * (abi.y + sc.wall_b);
+                    E += (double) pair_energy(wc, a, b, d2);
+                } else {
+                    E += (double) (0.5f * sc.wall_K * d2);
+                }
+            }
+        }
+    }
+
+    __shared__ double sh[BS / 32];
+    for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = E;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < BS / 32; w++) s += sh[w];
+        partials[blockIdx.x] = s;
+    }
+}
+
+__global__ void k_debug_noise(Params *Pp, int r, long long step, float *out)
+{
+    Params &P = *Pp;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    f3 z = normal3(P.st[r].seed, (uint32_t) i, step);
+    out[3 * i] = z.x;
+    out[3 * i + 1] = z.y;
+    out[3 * i + 2] = z.z;
+}
+
+// Squared radius of gyration of bead ranges [start, end): one block per range.
+__global__ void k_rg2(Params *Pp, int r, int n_ranges, const int *ranges, double *out)
+{
+    Params &P = *Pp;
+    int g = blockIdx.x;
+    if (g >= n_ranges) return;
+    const float4 *pos = P.pos[P.st[r].parity] + (size_t) r * P.n;
+    int s = ranges[2 * g], e = ranges[2 * g + 1];
+    double sx = 0, sy = 0, sz = 0, s2 = 0;
+    for (int i = s + threadIdx.x; i < e; i += blockDim.x) {
+        float4 p = pos[i];
+        sx += p.x; sy += p.y; sz += p.z;
+        s2 += (double) p.x * p.x + (double) p.y * p.y + (double) p.z * p.z;
+    }
+    __shared__ double sh[4][32];
+    double v[4] = {sx, sy, sz, s2};
+    for (int k = 0; k < 4; k++) {
+        for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        if ((threadIdx.x & 31) == 0) sh[k][threadIdx.x >> 5] = v[k];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a[4] = {0, 0, 0, 0};
+        for (int k = 0; k < 4; k++)
+            for (int w = 0; w < (int) (blockDim.x + 31) / 32; w++) a[k] += sh[k][w];
+        double m = (double) (e - s);
+        out[g] = m > 0 ? a[3] / m - (a[0] * a[0] + a[1] * a[1] + a[2] * a[2]) / (m * m) : 0.0;
+    }
+}
+
+} // namespace gc

@@ -1,0 +1,559 @@
+// gc_step.cuh -- force evaluation + BAOAB-limit Brownian update, fused.
+//
+// One thread owns one bead (in cell-sorted order) and GATHERS every term that
+// acts on it (full neighbour walk instead of the reference's half-list
+// scatter, MD/forcefield/neighbor_pairwise_forcefield.hpp:68-84), so there are
+// no force atomics and the result is bit-reproducible run to run.
+#pragma once
+
+#include "gc_kernels.cuh"
+
+namespace gc {
+
+enum StepMode : int {
+    STEP_FUSED = 0,   // force + update + per-step callback body (fixed dt)
+    STEP_FORCE = 1    // force only -> P.force (adaptive stepper, gc_compute_force)
+};
+
+// ---------------------------------------------------------------------------
+// FP64 context -> FP32 step constants (one thread, once per step per replica)
+// ---------------------------------------------------------------------------
+__device__ inline void refresh_consts(const Params &P, RepState &st)
+{
+    StepConst &c = st.sc;
+    {
+        double s = P.pair.scale_by_core ? st.core_scale : 1.0;
+        PairCoef pc = make_pair_coef(P.pair.eps_a, P.pair.sigma_a, P.pair.eps_b, P.pair.sigma_b, s,
+                                     P.pair.mode == PAIR_NONE ? PAIR_PLAIN : P.pair.mode);
+        c.kA2 = pc.kA2; c.kB2 = pc.kB2; c.cA = pc.cA; c.cB = pc.cB;
+        c.eA = pc.eA; c.eB = pc.eB; c.rc2 = pc.rc2;
+    }
+    if (P.wall.term >= 0) {
+        double s = P.wall.scale_by_core ? st.core_scale : 1.0;
+        // inward soft cores use HALF diameters
+        // (SIM/stage_interphase/simulation_driver_forcefield.cpp:214-221)
+        PairCoef wc = make_pair_coef(P.wall.eps_a, P.wall.sigma_a * 0.5, P.wall.eps_b,
+                                     P.wall.sigma_b * 0.5, s, PAIR_AB);
+        c.w_kA2 = wc.kA2; c.w_kB2 = wc.kB2; c.w_cA = wc.cA; c.w_cB = wc.cB;
+        c.w_eA = wc.eA; c.w_eB = wc.eB;
+        for (int k = 0; k < 3; k++) c.q[k] = (float) (1.0 / (st.semiaxes[k] * st.semiaxes[k]));
+        c.wall_a = (float) P.wall.wall_a;
+        c.wall_b = (float) P.wall.wall_b;
+        c.wall_K = (float) P.wall.outward_spring;
+    }
+    for (int b = 0; b < P.n_bond_terms; b++) {
+        const BondTerm &bt = P.bonds[b];
+        double s = bt.scale ? st.bond_scale : 1.0;
+        double is2 = 1.0 / (s * s);
+        c.bK_a[b] = (float) (bt.K_a * is2);
+        c.bK_b[b] = (float) (bt.K_b * is2);
+        c.bl_a[b] = (float) (bt.l_a * s);
+        c.bl_b[b] = (float) (bt.l_b * s);
+    }
+    for (int t = 0; t < P.n_triple_terms; t++) c.tE[t] = (float) P.triples[t].energy;
+    for (int k = 0; k < P.n_sources; k++) {
+        for (int d = 0; d < 3; d++) c.src_pt[k][d] = (float) P.sources[k].point[d];
+        c.src_p0[k] = (float) P.sources[k].p0;
+        c.src_p1[k] = (float) P.sources[k].p1;
+    }
+    for (int k = 0; k < P.n_poles; k++) {
+        for (int d = 0; d < 3; d++) c.pole[k][d] = (float) P.poles[k][d];
+    }
+    if (P.well.term >= 0) {
+        c.well_eps = (float) P.well.eps;
+        c.well_k2 = (float) (1.0 / (P.well.decay * P.well.decay));
+        c.well_cut2 = (float) (P.well.cutoff * P.well.cutoff);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// per-bead force: all enabled terms acting on the bead in sorted slot t
+// ---------------------------------------------------------------------------
+struct WallAcc {
+    float ax, ay, az, reaction;
+};
+
+__device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, int r, int t,
+                                         int idx, float4 self4, float2 abi, unsigned mask,
+                                         WallAcc &wacc)
+{
+    const StepConst &sc = st.sc;
+    const size_t ro = (size_t) r * P.n;
+    const int par = st.parity;
+    const f3 self = make_f3(self4);
+    f3 F = {0.0f, 0.0f, 0.0f};
+
+    // ---- nonbonded soft cores over the neighbouring cell rows -------------
+    if (P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u)) {
+        PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
+        const bool plain = P.pair.mode == PAIR_PLAIN;
+        const float4 *__restrict__ sp = P.spos[par] + ro;
+        const float2 *__restrict__ sab = P.sab + ro;
+        const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+        const int dx = st.dims[0], dy = st.dims[1], dz = st.dims[2];
+        const int M = P.cells_per_cut;
+        int c = P.scell[ro + t];
+        int cx = c % dx, cy = (c / dx) % dy, cz = c / (dx * dy);
+        int x0 = max(cx - M, 0), x1 = min(cx + M, dx - 1);
+        for (int z = max(cz - M, 0); z <= min(cz + M, dz - 1); z++) {
+            for (int y = max(cy - M, 0); y <= min(cy + M, dy - 1); y++) {
+                int row = dx * (y + dy * z);
+                int lo = start[row + x0], hi = start[row + x1 + 1];
+                for (int j = lo; j < hi; j++) {
+                    float4 q = __ldg(&sp[j]);
+                    f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
+                    float r2 = dot(d, d);
+                    if (r2 < pc.rc2) {
+                        // the bead itself has d = 0 and contributes exactly 0
+                        float a = 1.0f, b = 0.0f;
+                        if (!plain) {
+                            float2 abj = __ldg(&sab[j]);
+                            a = 0.5f * (abi.x + abj.x);
+                            b = 0.5f * (abi.y + abj.y);
+                        }
+                        float fac = pair_force_factor(pc, a, b, r2);
+                        F.x = fmaf(fac, d.x, F.x);
+                        F.y = fmaf(fac, d.y, F.y);
+                        F.z = fmaf(fac, d.z, F.z);
+                    }
+                }
+            }
+        }
+    }
+
+    const float4 *__restrict__ pos = P.pos[par] + ro;   // original order
+    const int flags = P.flags[idx];
+
+    // ---- bonded pairs (MD/forcefield/bonded_pairwise_forcefield.hpp:78-93) -
+    {
+        int e0 = P.bond_off[idx], e1 = P.bond_off[idx + 1];
+        for (int e = e0; e < e1; e++) {
+            BondEntry be = P.bond_ent[e];
+            const BondTerm &bt = P.bonds[be.bterm];
+            if (!(mask >> bt.term & 1u)) continue;
+            float4 q = pos[be.partner];
+            f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
+            float K = sc.bK_a[be.bterm], l = sc.bl_a[be.bterm];
+            if (bt.mix_ab) {
+                float2 abj = P.ab[be.partner];
+                float a = 0.5f * (abi.x + abj.x), b = 0.5f * (abi.y + abj.y);
+                K = a * sc.bK_a[be.bterm] + b * sc.bK_b[be.bterm];
+                l = a * sc.bl_a[be.bterm] + b * sc.bl_b[be.bterm];
+            }
+            float fac = bond_force_factor(bt.kind, K, l, dot(d, d));
+            F.x = fmaf(fac, d.x, F.x);
+            F.y = fmaf(fac, d.y, F.y);
+            F.z = fmaf(fac, d.z, F.z);
+        }
+    }
+
+    // ---- bending triples (MD/forcefield/bonded_triplewise_forcefield.hpp) --
+    if (flags & 1) {
+        int e0 = P.triple_off[idx], e1 = P.triple_off[idx + 1];
+        for (int e = e0; e < e1; e++) {
+            TripleEntry te = P.triple_ent[e];
+            int tt = te.role_term >> 2, role = te.role_term & 3;
+            if (!(mask >> P.triples[tt].term & 1u)) continue;
+            f3 pi = make_f3(pos[te.i]), pj = make_f3(pos[te.j]), pk = make_f3(pos[te.k]);
+            f3 f = bending_force(sc.tE[tt], pi - pj, pj - pk, role);
+            F = F + f;
+        }
+    }
+
+    // ---- kinetochore fibres (SIM/common/forcefield/kinetochore_fiber_forcefield.cpp:70-84)
+    if (flags & 2) {
+        int e0 = P.tether_off[idx], e1 = P.tether_off[idx + 1];
+        for (int e = e0; e < e1; e++) {
+            TetherEntry te = P.tether_ent[e];
+            if (!(mask >> te.term & 1u)) continue;
+            f3 d = {self.x - sc.pole[te.pole][0], self.y - sc.pole[te.pole][1],
+                    self.z - sc.pole[te.pole][2]};
+            float fac = bond_force_factor(2 /* GC_BOND_SPRING */, te.spring, te.length, dot(d, d));
+            F = F + fac * d;
+        }
+    }
+
+    // ---- nucleolar droplet: brute force over the (few) target beads --------
+    if ((flags & 4) && P.well.term >= 0 && (mask >> P.well.term & 1u)) {
+        for (int k = 0; k < P.well.n_targets; k++) {
+            int j = P.well.targets[k];
+            if (j == idx) continue;
+            float4 q = pos[j];
+            f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
+            float fac = well_force_factor(sc.well_eps, sc.well_k2, sc.well_cut2, dot(d, d));
+            F = F + fac * d;
+        }
+    }
+
+    // ---- point sources (MD/forcefield/point_source_forcefield.hpp:88-110) --
+    for (int k = 0; k < P.n_sources; k++) {
+        if (!(mask >> P.sources[k].term & 1u)) continue;
+        f3 d = {self.x - sc.src_pt[k][0], self.y - sc.src_pt[k][1], self.z - sc.src_pt[k][2]};
+        float r2 = dot(d, d);
+        float fac = P.sources[k].kind == 0
+                        ? bond_force_factor(0, sc.src_p0[k], sc.src_p1[k], r2)
+                        : flux_force_factor(sc.src_p0[k], sc.src_p1[k], r2);
+        F = F + fac * d;
+    }
+
+    // ---- ellipsoidal wall, inward + outward fused --------------------------
+    // MD/forcefield/ellipsoid_surface_forcefield.hpp:55-211.  The potential is
+    // central in delta, so iso = f and aniso = 0 and the reference's
+    // iso + (aniso - iso) o strain reduces to f o (1 - strain).
+    if (P.wall.term >= 0 && (mask >> P.wall.term & 1u)) {
+        f3 dual = {sc.q[0] * self.x, sc.q[1] * self.y, sc.q[2] * self.z};
+        float dd = dot(dual, dual);
+        if (dd != 0.0f) {
+            float phi = fmaf(dual.x, self.x, fmaf(dual.y, self.y, fmaf(dual.z, self.z, -1.0f)));
+            float kappa = phi / (2.0f * dd);
+            f3 delta = kappa * dual;
+            float d2 = dot(delta, delta);
+            float fac;
+            if (phi < 0.0f) {
+                PairCoef wc = {sc.w_kA2, sc.w_kB2, sc.w_cA, sc.w_cB, sc.w_eA, sc.w_eB, 0.0f};
+                float a = 0.5f * (abi.x + sc.wall_a), b = 0.5f * (abi.y + sc.wall_b);
+                fac = pair_force_factor(wc, a, b, d2);
+            } else {
+                fac = -sc.wall_K;
+            }
+            f3 f = {fac * delta.x * (1.0f - kappa * sc.q[0]),
+                    fac * delta.y * (1.0f - kappa * sc.q[1]),
+                    fac * delta.z * (1.0f - kappa * sc.q[2])};
+            F = F + f;
+            // statistics (ellipsoid_surface_forcefield.hpp:199-209): the outward
+            // normal has the sign of the bead coordinate on every axis.
+            wacc.ax -= self.x > 0.0f ? f.x : -f.x;
+            wacc.ay -= self.y > 0.0f ? f.y : -f.y;
+            wacc.az -= self.z > 0.0f ? f.z : -f.z;
+            if (d2 > 0.0f) {
+                float sgn = phi < 0.0f ? -1.0f : 1.0f;
+                wacc.reaction -= sgn * dot(f, delta) * rsqrtf(d2);
+            }
+        }
+    }
+    return F;
+}
+
+// ---------------------------------------------------------------------------
+// block reductions
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float warp_max(float v)
+{
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_min(float v)
+{
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ long long warp_sum(long long v)
+{
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+struct StepRed {          // per-thread contributions to the per-step reductions
+    float lo[3], hi[3];   // bounding box of the new positions
+    float disp2;          // squared displacement from the rebuild reference
+    float dtmin;          // adaptive time-step candidate
+    WallAcc w;
+    bool bad;
+};
+
+__device__ __forceinline__ void red_init(StepRed &s)
+{
+    for (int k = 0; k < 3; k++) { s.lo[k] = INFINITY; s.hi[k] = -INFINITY; }
+    s.disp2 = 0.0f;
+    s.dtmin = INFINITY;
+    s.w = {0.0f, 0.0f, 0.0f, 0.0f};
+    s.bad = false;
+}
+
+// Reduce over the block, push one set of atomics per block, take a ticket.
+// Returns true in every thread of the LAST block of this replica.
+template<int NT>
+__device__ __forceinline__ bool block_reduce_commit(RepState &st, StepRed &s, bool with_wall,
+                                                    bool with_geom, bool with_dt)
+{
+    constexpr int NW = NT / 32;
+    __shared__ float sh_f[NW][8];
+    __shared__ long long sh_l[NW][4];
+    __shared__ int sh_bad, sh_last;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) sh_bad = 0;
+
+    float v[8];
+    for (int k = 0; k < 3; k++) { v[k] = warp_min(s.lo[k]); v[3 + k] = warp_max(s.hi[k]); }
+    v[6] = warp_max(s.disp2);
+    v[7] = warp_min(s.dtmin);
+    long long q[4];
+    q[0] = warp_sum(__double2ll_rn((double) s.w.ax * GC_FX_SCALE));
+    q[1] = warp_sum(__double2ll_rn((double) s.w.ay * GC_FX_SCALE));
+    q[2] = warp_sum(__double2ll_rn((double) s.w.az * GC_FX_SCALE));
+    q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
+    bool bad = __any_sync(0xffffffffu, s.bad);
+    __syncthreads();
+    if (lane == 0) {
+        for (int k = 0; k < 8; k++) sh_f[wid][k] = v[k];
+        for (int k = 0; k < 4; k++) sh_l[wid][k] = q[k];
+        if (bad) sh_bad = 1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < NW; w++) {
+            for (int k = 0; k < 3; k++) {
+                v[k] = fminf(v[k], sh_f[w][k]);
+                v[3 + k] = fmaxf(v[3 + k], sh_f[w][3 + k]);
+            }
+            v[6] = fmaxf(v[6], sh_f[w][6]);
+            v[7] = fminf(v[7], sh_f[w][7]);
+            for (int k = 0; k < 4; k++) q[k] += sh_l[w][k];
+        }
+        if (with_geom) {
+            for (int k = 0; k < 3; k++) {
+                atomicMin(&st.bbox_min[k], float_to_ordered(v[k]));
+                atomicMax(&st.bbox_max[k], float_to_ordered(v[3 + k]));
+            }
+            // NaN displacement: bits compare above every finite value
+            atomicMax(&st.maxdisp2_bits, __float_as_uint(v[6] != v[6] ? NAN : v[6]));
+        }
+        if (with_dt) atomicMin(&st.dtmin_bits, __float_as_uint(v[7]));
+        if (with_wall) {
+            for (int k = 0; k < 3; k++) {
+                if (q[k]) atomicAdd((unsigned long long *) &st.axial_fx[k], (unsigned long long) q[k]);
+            }
+            if (q[3]) atomicAdd((unsigned long long *) &st.reaction_fx, (unsigned long long) q[3]);
+        }
+        if (sh_bad) atomicExch(&st.error, 1);
+        __threadfence();
+        unsigned int prev = atomicAdd(&st.ticket, 1u);
+        sh_last = prev == gridDim.x - 1;
+        if (sh_last) __threadfence();
+    }
+    __syncthreads();
+    return sh_last != 0;
+}
+
+// Wall statistics of the force pass just finished: fixed point -> double.
+__device__ inline void finalize_stats(RepState &st)
+{
+    volatile long long *fx = st.axial_fx;
+    for (int k = 0; k < 3; k++) {
+        st.axial[k] = (double) fx[k] / GC_FX_SCALE;
+        st.axial_fx[k] = 0;
+    }
+    st.reaction = (double) *(volatile long long *) &st.reaction_fx / GC_FX_SCALE;
+    st.reaction_fx = 0;
+}
+
+// The body of the driver's per-step callback plus list maintenance, executed by
+// one thread of the last block after every bead has been updated:
+//   SIM/stage_interphase/simulation_driver_interphase.cpp:16-18 (time),
+//   67-76 (core/bond scale, contact distance), 79-90 (wall ODE)
+//   MD/forcefield/detail/neighbor_list.hpp:101-159 (consistency check)
+__device__ inline void finalize_step(const Params &P, RepState &st, double dt_used)
+{
+    st.dt_prev = st.dt_last;
+    st.dt_last = dt_used;
+    st.step += 1;
+    st.time = (double) st.step * (double) P.dt;
+
+    st.contact_distance_prev = st.contact_distance;
+    if (P.sched.enabled) {
+        st.core_scale = 1.0 - (1.0 - P.sched.core_init) * exp(-st.time / P.sched.core_tau);
+        st.bond_scale = 1.0 - (1.0 - P.sched.bond_init) * exp(-st.time / P.sched.bond_tau);
+    }
+    if (P.contact.enabled && P.contact.scale_by_core) {
+        st.contact_distance = P.contact.base_distance * st.core_scale;
+    }
+    if (P.wall.term >= 0 && P.wall.ode_enabled) {
+        for (int k = 0; k < 3; k++) {
+            double net = st.axial[k] - P.wall.ode_spring[k] * st.semiaxes[k];
+            st.semiaxes[k] += (double) P.dt * P.wall.ode_mobility * net;
+        }
+    }
+    st.parity ^= 1;
+
+    // list maintenance for the NEXT force evaluation
+    float maxdisp2 = __uint_as_float(*(volatile unsigned int *) &st.maxdisp2_bits);
+    if (maxdisp2 != maxdisp2) st.error = 1;
+    double rnow = interaction_radius(P, st);
+    bool need = P.skin <= 0.0f || !(rnow + 2.0 * sqrt((double) maxdisp2) <= (double) st.rc_valid);
+    if (need) {
+        // bbox was accumulated from the positions just written
+        int bmin[3], bmax[3];
+        for (int k = 0; k < 3; k++) {
+            bmin[k] = *(volatile int *) &st.bbox_min[k];
+            bmax[k] = *(volatile int *) &st.bbox_max[k];
+        }
+        for (int k = 0; k < 3; k++) { st.bbox_min[k] = bmin[k]; st.bbox_max[k] = bmax[k]; }
+        plan_grid(P, st, rnow * (1.0 + (double) P.skin));
+        st.need_rebuild = 1;
+        st.maxdisp2_bits = 0u;
+        st.rebuilds += 1;
+    } else {
+        st.need_rebuild = 0;
+    }
+    for (int k = 0; k < 3; k++) {
+        st.bbox_min[k] = 0x7fffffff;
+        st.bbox_max[k] = (int) 0x80000000;
+    }
+    st.dtmin_bits = 0x7f800000u;
+    st.ticket = 0u;
+    refresh_consts(P, st);
+}
+
+// ---------------------------------------------------------------------------
+// BAOAB-limit update of one bead
+//   MD/simulation/detail/brownian_simulator.hpp:61-75:
+//     x += mu dt F;  x += (W_n + W_{n-1}) / 2;  W = sqrt(2 kT mu dt) N(0,1)^3
+//   W_{n-1} is REGENERATED from the counter-based stream instead of stored.
+//   The two increments are summed first so x is rounded once in FP32.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ f3 bead_noise(const Params &P, const RepState &st, int r, int idx,
+                                         long long n)
+{
+    if (P.noise) {
+        const float *z = P.noise + (((size_t) r * P.noise_steps + (size_t) (n - 1 - P.noise_step0)) *
+                                        P.n + idx) * 3;
+        return {z[0], z[1], z[2]};
+    }
+    return normal3(st.seed, (uint32_t) idx, n);
+}
+
+__device__ __forceinline__ void integrate_bead(const Params &P, const RepState &st, int r, int t,
+                                               int idx, float4 self4, f3 F, float dt,
+                                               float dt_prev, StepRed &red)
+{
+    const size_t ro = (size_t) r * P.n;
+    const int par = st.parity;
+    const long long n = st.step + 1;
+    float mu = P.mob[idx];
+    float mudt = dt * mu;
+    float sigma = sqrtf(2.0f * P.kT * mudt);
+    f3 W = sigma * bead_noise(P, st, r, idx, n);
+    f3 Wp = {0.0f, 0.0f, 0.0f};
+    if (n > 1) {
+        float sigma_p = sqrtf(2.0f * P.kT * dt_prev * mu);
+        Wp = sigma_p * bead_noise(P, st, r, idx, n - 1);
+    }
+    float4 x;
+    x.x = self4.x + fmaf(mudt, F.x, 0.5f * (W.x + Wp.x));
+    x.y = self4.y + fmaf(mudt, F.y, 0.5f * (W.y + Wp.y));
+    x.z = self4.z + fmaf(mudt, F.z, 0.5f * (W.z + Wp.z));
+    x.w = 0.0f;
+    P.pos[par ^ 1][ro + idx] = x;
+    x.w = self4.w;
+    P.spos[par ^ 1][ro + t] = x;
+
+    float4 ref = P.sref[ro + t];
+    float ex = x.x - ref.x, ey = x.y - ref.y, ez = x.z - ref.z;
+    red.disp2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+    red.lo[0] = red.hi[0] = x.x;
+    red.lo[1] = red.hi[1] = x.y;
+    red.lo[2] = red.hi[2] = x.z;
+    red.bad = !(fabsf(x.x) < INFINITY && fabsf(x.y) < INFINITY && fabsf(x.z) < INFINITY);
+}
+
+// MD/simulation/detail/brownian_timestepper.hpp:72-91 (root in the
+// cancellation-free form 2c / (b + sqrt(b^2 + 4ac)))
+__device__ __forceinline__ float solve_timestep(float spacestep, float mu, float f2, float kT,
+                                                float dt_max)
+{
+    if (mu == 0.0f && f2 == 0.0f) return dt_max;
+    float a = mu * mu * f2;
+    float b = 2.55f * mu * kT;
+    float c = spacestep * spacestep;
+    if (a * c < 1.0e-6f * b * b) return c / b;
+    return 2.0f * c / (b + sqrtf(fmaf(b, b, 4.0f * a * c)));
+}
+
+// ---------------------------------------------------------------------------
+// step kernels
+// ---------------------------------------------------------------------------
+template<int MODE>
+__global__ void __launch_bounds__(BS) k_step(Params *Pp, unsigned mask_arg, int use_enabled)
+{
+    Params &P = *Pp;
+    const int r = blockIdx.y;
+    RepState &st = P.st[r];
+    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
+    const int t = blockIdx.x * BS + threadIdx.x;
+    StepRed red;
+    red_init(red);
+
+    if (t < P.n) {
+        const size_t ro = (size_t) r * P.n;
+        float4 self4 = P.spos[st.parity][ro + t];
+        int idx = __float_as_int(self4.w);
+        float2 abi = P.sab[ro + t];
+        f3 F = bead_force(P, st, r, t, idx, self4, abi, mask, red.w);
+        if (MODE == STEP_FORCE) {
+            P.force[ro + idx] = make_float4(F.x, F.y, F.z, 0.0f);
+            if (P.spacestep != 0.0f) {
+                red.dtmin = solve_timestep(P.spacestep, P.mob[idx], dot(F, F), P.kT, P.dt);
+            }
+            red.bad = !(fabsf(F.x) < INFINITY && fabsf(F.y) < INFINITY && fabsf(F.z) < INFINITY);
+        } else {
+            integrate_bead(P, st, r, t, idx, self4, F, P.dt, P.dt, red);
+        }
+    }
+
+    bool last = block_reduce_commit<BS>(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
+    if (last && threadIdx.x == 0) {
+        finalize_stats(st);
+        if (MODE == STEP_FUSED) {
+            finalize_step(P, st, (double) P.dt);
+        } else {
+            float dtc = P.dt;
+            if (P.spacestep != 0.0f) {
+                dtc = fminf(dtc, __uint_as_float(*(volatile unsigned int *) &st.dtmin_bits));
+            }
+            st.sc.dt_cur = dtc;
+            st.dtmin_bits = 0x7f800000u;
+            st.ticket = 0u;
+        }
+    }
+}
+
+// Second half of an adaptive step: update with the globally reduced dt.
+__global__ void __launch_bounds__(BS) k_integrate(Params *Pp)
+{
+    Params &P = *Pp;
+    const int r = blockIdx.y;
+    RepState &st = P.st[r];
+    const int t = blockIdx.x * BS + threadIdx.x;
+    StepRed red;
+    red_init(red);
+    const float dt = st.sc.dt_cur;
+
+    if (t < P.n) {
+        const size_t ro = (size_t) r * P.n;
+        float4 self4 = P.spos[st.parity][ro + t];
+        int idx = __float_as_int(self4.w);
+        float4 F4 = P.force[ro + idx];
+        f3 F = {F4.x, F4.y, F4.z};
+        integrate_bead(P, st, r, t, idx, self4, F, dt, (float) st.dt_last, red);
+    }
+    bool last = block_reduce_commit<BS>(st, red, false, true, false);
+    if (last && threadIdx.x == 0) finalize_step(P, st, (double) dt);
+}
+
+// radius_override > 0 forces the list radius (gc_neighbor_pairs).
+__global__ void k_plan(Params *Pp, double radius_override)
+{
+    Params &P = *Pp;
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= P.n_rep) return;
+    RepState &st = P.st[r];
+    double rl = radius_override > 0.0 ? radius_override
+                                      : interaction_radius(P, st) * (1.0 + (double) P.skin);
+    plan_grid(P, st, rl);
+    st.need_rebuild = 1;
+    st.maxdisp2_bits = 0u;
+    st.rebuilds += 1;
+    refresh_consts(P, st);
+}
+
+} // namespace gc

@@ -1,0 +1,192 @@
+// gc_types.cuh -- device-visible data structures of the B200 hot path.
+//
+// Layout in HBM (R replicas x N beads, one context per GPU):
+//   pos [2][R][N] float4   positions in ORIGINAL bead order, ping-pong by step parity
+//   spos[2][R][N] float4   positions in CELL-SORTED order (w = original index bits)
+//   sref   [R][N] float4   sorted positions at the last rebuild (skin check)
+//   sidx / scell / slot_of [R][N] int32  sorted<->original maps, cell of each slot
+//   sab    [R][N] float2   (a, b) factors gathered into sorted order
+//   cell_count / cell_start [R][ncell_max(+1)] int32
+//   force  [R][N] float4   only for the adaptive stepper / gc_compute_force
+//   st     [R]    RepState per-replica scalars (schedule, wall, reductions)
+// Bead attributes and bonded topology are shared by all replicas.
+#pragma once
+
+#include <cstdint>
+
+#include <cuda_runtime.h>
+
+#define GC_MAX_BOND_TERMS 8
+#define GC_MAX_TRIPLE_TERMS 4
+#define GC_MAX_SOURCES 4
+#define GC_MAX_POLES 4
+
+// fixed-point scale of the wall-reaction accumulators (deterministic sums)
+#define GC_FX_SCALE 4294967296.0 /* 2^32 */
+
+namespace gc {
+
+enum PairMode : int { PAIR_NONE = 0, PAIR_AB = 1, PAIR_PLAIN = 2 };
+
+struct PairParams {
+    int mode;           // PairMode
+    int term;           // term id (enable bit)
+    int scale_by_core;
+    int pad;
+    double eps_a, sigma_a, eps_b, sigma_b;
+};
+
+struct WellParams {     // nucleolar droplet, softwell<6> + cutoff on targets
+    int term;           // -1 = absent
+    int n_targets;
+    const int *targets; // device
+    double eps, decay, cutoff;
+};
+
+struct BondTerm {
+    int kind, mix_ab, scale, term;
+    double K_a, K_b, l_a, l_b;
+};
+
+struct TripleTerm {
+    int term, pad;
+    double energy;
+};
+
+struct SourceTerm {
+    int kind, term;
+    double point[3];
+    double p0, p1;
+};
+
+struct WallParams {
+    int term;           // -1 = absent
+    int scale_by_core;
+    int ode_enabled;
+    int pad;
+    double eps_a, sigma_a, eps_b, sigma_b, wall_a, wall_b, outward_spring;
+    double ode_mobility;
+    double ode_spring[3];
+};
+
+struct Schedule {
+    int enabled, pad;
+    double core_init, core_tau, bond_init, bond_tau;
+};
+
+struct ContactParams {
+    double base_distance;
+    long long interval;
+    int scale_by_core;
+    int enabled;
+    unsigned long long *keys; // [R][capacity]
+    unsigned int *vals;       // [R][capacity]
+    unsigned long long capacity; // power of two, per replica
+    unsigned int *used;       // [R] distinct keys inserted
+};
+
+// Per-bead bonded adjacency (gather form: every bead sums its own terms, no
+// atomics, deterministic).
+struct BondEntry { int partner; int bterm; };          // bterm indexes Params::bonds
+struct TripleEntry { int i, j, k; int role_term; };    // role (0,1,2) | tterm << 2
+struct TetherEntry { int pole; float spring; float length; int term; };
+
+// FP32 constants of one step, derived from the FP64 context by the last block
+// of the previous step (refresh_consts) so that no per-bead FP64 work is needed.
+struct StepConst {
+    float kA2, kB2, cA, cB, eA, eB, rc2;          // pair soft cores (PairCoef)
+    float w_kA2, w_kB2, w_cA, w_cB, w_eA, w_eB;   // wall inward soft cores (half diameters)
+    float q[3];                                   // 1 / semiaxis^2
+    float wall_a, wall_b, wall_K;
+    float bK_a[GC_MAX_BOND_TERMS], bK_b[GC_MAX_BOND_TERMS];
+    float bl_a[GC_MAX_BOND_TERMS], bl_b[GC_MAX_BOND_TERMS];
+    float tE[GC_MAX_TRIPLE_TERMS];
+    float src_pt[GC_MAX_SOURCES][3], src_p0[GC_MAX_SOURCES], src_p1[GC_MAX_SOURCES];
+    float pole[GC_MAX_POLES][3];
+    float well_eps, well_k2, well_cut2;
+    float dt_cur;                                 // dt of the step in flight
+    float pad;
+};
+
+// Per-replica mutable scalars.  Written only by the last block of a step (or
+// by the host between runs); read by every block at kernel start.
+struct RepState {
+    // --- context (double, as the reference's interphase_context) ---
+    double time;
+    double core_scale, bond_scale;
+    double semiaxes[3];
+    double contact_distance;       // used by the next explicit update
+    double contact_distance_prev;  // value in force during the last callback
+    double axial[3], reaction;     // wall statistics of the last force pass
+    double dt_last;                // dt used by the last step
+    double dt_prev;                // dt of the step before (Wiener regeneration)
+    long long step;                // steps done in this logical run
+    long long rebuilds;
+    unsigned long long seed;
+    // --- per-step reductions (reset by the last block) ---
+    long long axial_fx[3], reaction_fx;
+    unsigned int maxdisp2_bits;    // max |x - x_ref|^2 since rebuild (float bits)
+    unsigned int dtmin_bits;       // adaptive dt candidate (float bits)
+    int bbox_min[3], bbox_max[3];  // order-preserving int encoding of floats
+    unsigned int ticket;
+    // --- cell grid ---
+    int need_rebuild;
+    int parity;                    // which ping-pong buffer holds current positions
+    int dims[3];
+    int ncell;
+    float origin[3];
+    float cell_size, inv_cell;
+    float rc_valid;                // interaction radius the current cells guarantee
+    int error;                     // sticky: 1 = NaN/Inf seen
+    int pad;
+    StepConst sc;
+};
+
+struct Params {
+    int n, n_rep;
+    int ncell_max;
+    int cells_per_cut;             // M: cell edge = r_list / M
+    float skin;                    // fraction of the cutoff
+    float kT;
+    float dt;                      // configured dt (dt_max in adaptive mode)
+    float spacestep;
+    unsigned int enabled;          // term enable bits
+
+    // shared attributes
+    const float *mob;              // [N]
+    const float2 *ab;              // [N]
+    const int *flags;              // [N] bit0 triples, bit1 tethers, bit2 droplet target
+    const int *bond_off;           // [N+1]
+    const BondEntry *bond_ent;
+    const int *triple_off;         // [N+1]
+    const TripleEntry *triple_ent;
+    const int *tether_off;         // [N+1]
+    const TetherEntry *tether_ent;
+
+    // per-replica state
+    float4 *pos[2];
+    float4 *spos[2];
+    float4 *sref;
+    int *sidx, *scell, *slot_of;
+    float2 *sab;
+    int *cell_count, *cell_start, *members, *cell_of;
+    float4 *force;
+    RepState *st;
+    const float *noise;            // injected normals [R][steps][N][3] or null
+    long long noise_steps;         // steps covered by `noise`
+    long long noise_step0;         // st->step value that maps to noise row 0
+
+    // terms
+    PairParams pair;
+    WellParams well;
+    WallParams wall;
+    Schedule sched;
+    ContactParams contact;
+    int n_bond_terms, n_triple_terms, n_sources, n_poles;
+    BondTerm bonds[GC_MAX_BOND_TERMS];
+    TripleTerm triples[GC_MAX_TRIPLE_TERMS];
+    SourceTerm sources[GC_MAX_SOURCES];
+    double poles[GC_MAX_POLES][3];
+};
+
+} // namespace gc

@@ -1,0 +1,260 @@
+/*
+ * gc_b200.h -- C-ABI of the B200-native force-evaluation + overdamped-Langevin
+ * hot path that sits behind 3d-genome-cycle's src/simulation stage drivers.
+ *
+ * Every entry point names the reference interface it replaces.  Citations are
+ * relative to the reference tree; MD/ = submodules/github.com/snsinfu/micromd/
+ * include/md/, SIM/ = src/simulation/.
+ *
+ * Conventions
+ *   - plain pointers and sizes, no C++/torch types; host arrays are copied in/out
+ *   - every function returns GC_OK (0) or a negative gc_status; the message is
+ *     available from gc_last_error().  Nothing throws across this boundary.
+ *     (The reference signals errors with C++ exceptions)
+ *   - one gc_ctx = one CUDA device + one stream + R replicas that share bead
+ *     attributes and topology and differ in positions / seed / context.
+ *   - term-adding functions return a term id >= 0 usable with
+ *     gc_set_term_enabled() and as bit (1u << id) in force/energy masks.
+ */
+#ifndef GC_B200_H
+#define GC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gc_ctx gc_ctx;
+
+typedef enum gc_status {
+    GC_OK = 0,
+    GC_ERR_INVALID = -1,   /* bad argument */
+    GC_ERR_CUDA = -2,      /* CUDA runtime failure (message has the string) */
+    GC_ERR_STATE = -3,     /* call out of order (e.g. run before attrs) */
+    GC_ERR_NUMERIC = -4,   /* NaN/Inf position detected on device */
+    GC_ERR_CAPACITY = -5   /* contact table / output buffer too small */
+} gc_status;
+
+#define GC_MAX_TERMS 32
+#define GC_MASK_ALL 0xffffffffu
+
+/* Bond potentials (MD/potential/{semispring,harmonic,spring}_potential.hpp). */
+typedef enum gc_bond_kind {
+    GC_BOND_SEMISPRING = 0, /* F = (K l / r - K) r_vec for r > l, else 0 */
+    GC_BOND_HARMONIC = 1,   /* F = -K r_vec */
+    GC_BOND_SPRING = 2      /* F = (K l / r - K) r_vec, 0 at r == 0 */
+} gc_bond_kind;
+
+/*
+ * Parameters of one bonded-pair force field.
+ *   mix_ab = 1: K = a K_a + b K_b, l = a l_a + b l_b with a, b the arithmetic
+ *               means of the two beads' A/B factors
+ *               (SIM/stage_interphase/simulation_driver_forcefield.cpp:56-96);
+ *   mix_ab = 0: K = K_a, l = l_a.
+ *   scale  = 1: K <- K / s^2, l <- l s with s = bond_scale(t) (same file, 83-85).
+ */
+typedef struct gc_bond_params {
+    int32_t kind;
+    int32_t mix_ab;
+    int32_t scale;
+    int32_t reserved;
+    double K_a, K_b, l_a, l_b;
+} gc_bond_params;
+
+/* Point-source potentials (MD/forcefield/point_source_forcefield.hpp:34-147). */
+typedef enum gc_source_kind {
+    GC_SOURCE_SEMISPRING = 0, /* p0 = K, p1 = l  (telophase packing) */
+    GC_SOURCE_FORCE_FLUX = 1  /* p0 = f, p1 = b  (polar ejection,
+                                 SIM/common/potentials/force_flux_potential.hpp:19-38) */
+} gc_source_kind;
+
+/*
+ * Ellipsoidal nuclear wall: inward A/B-mixed soft core + outward harmonic,
+ * optionally moving under the wall ODE
+ * (SIM/stage_interphase/simulation_driver_forcefield.cpp:189-244,
+ *  SIM/stage_interphase/simulation_driver_interphase.cpp:79-90).
+ * The inward soft-core diameters are HALF of sigma_a / sigma_b and scale with
+ * core_scale(t) when scale_by_core is set.
+ */
+typedef struct gc_wall_params {
+    double semiaxes[3];
+    double eps_a, sigma_a, eps_b, sigma_b; /* full bead diameters */
+    double wall_a, wall_b;                 /* wall_ab_factor */
+    double outward_spring;                 /* wall_packing_spring */
+    int32_t scale_by_core;
+    int32_t ode_enabled;                   /* move semiaxes each step */
+    double ode_mobility;                   /* wall_mobility */
+    double ode_spring[3];                  /* wall_semiaxes_spring */
+} gc_wall_params;
+
+/*
+ * Per-step parameter schedule evaluated on device after every step
+ * (SIM/stage_interphase/simulation_driver_interphase.cpp:67-76):
+ *   core_scale = 1 - (1 - core_init) exp(-t / core_tau), same for bond_scale.
+ */
+typedef struct gc_schedule {
+    int32_t enabled;
+    int32_t reserved;
+    double core_init, core_tau, bond_init, bond_tau;
+} gc_schedule;
+
+/* Mutable per-replica global state (SIM/common/simulation_context.hpp:7-18). */
+typedef struct gc_context {
+    double time;
+    double semiaxes[3];
+    double core_scale;
+    double bond_scale;
+    double contact_distance;   /* distance used by the NEXT contact update */
+    double axial_reaction[3];  /* sum of inward+outward stats of last force call */
+    double reaction_force;
+    double last_timestep;      /* dt used by the last step (adaptive mode) */
+    int64_t step;              /* steps done in the current logical run */
+    int64_t rebuilds;          /* cell-list rebuilds so far */
+} gc_context;
+
+/*
+ * One call of md::simulate_brownian_dynamics
+ * (MD/simulation/brownian_dynamics.hpp:24-73), possibly split in chunks.
+ */
+typedef struct gc_run_config {
+    int64_t steps;        /* steps to run in this call */
+    double temperature;
+    double timestep;      /* dt, or dt_max when spacestep != 0 */
+    double spacestep;     /* != 0 selects the adaptive time stepper */
+    int32_t restart;      /* 1: first chunk of a logical run: zero the Wiener
+                             history and the step counter (the reference's
+                             integrator state lives for one call only) */
+    int32_t reserved;
+    /* Test mode: injected standard normals, [steps][n_beads][3] doubles for
+       replica 0 .. R-1 consecutively ([R][steps][N][3]); NULL = Philox. */
+    const double *noise;
+} gc_run_config;
+
+/* ---- lifetime ---------------------------------------------------------- */
+
+/* Replaces md::system construction + add_particle (MD/system.hpp:60-140). */
+int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out);
+int gc_destroy(gc_ctx *ctx);
+const char *gc_last_error(const gc_ctx *ctx);
+/* Library build info ("gc_b200 <ver> sm_100a"). */
+const char *gc_version(void);
+
+/* ---- beads ------------------------------------------------------------- */
+
+/* view_mobilities() + view(particle_data_attribute)
+   (SIM/stage_interphase/simulation_driver_particles.cpp:8-35).
+   a_factor / b_factor may be NULL (all zero). Shared by all replicas. */
+int gc_set_bead_attrs(gc_ctx *ctx, const double *mobility, const double *a_factor,
+                      const double *b_factor);
+/* view_positions() write / read, xyz = [n_beads][3]. replica = -1 on set
+   broadcasts to every replica. */
+int gc_set_positions(gc_ctx *ctx, int32_t replica, const double *xyz);
+int gc_get_positions(gc_ctx *ctx, int32_t replica, double *xyz);
+int gc_set_positions_f32(gc_ctx *ctx, int32_t replica, const float *xyz);
+int gc_get_positions_f32(gc_ctx *ctx, int32_t replica, float *xyz);
+/* Philox key per replica (the drivers draw it from mt19937_64(design.seed),
+   SIM/stage_interphase/simulation_driver_interphase.cpp:61). */
+int gc_set_seeds(gc_ctx *ctx, const uint64_t *seeds);
+
+/* ---- force-field terms ------------------------------------------------- */
+
+/* make_neighbor_pairwise_forcefield(a*softcore<2,3> + b*softcore<8,3>)
+   (SIM/stage_interphase/simulation_driver_forcefield.cpp:20-53). */
+int gc_add_pair_softcore_ab(gc_ctx *ctx, double eps_a, double sigma_a, double eps_b,
+                            double sigma_b, int32_t scale_by_core);
+/* make_neighbor_pairwise_forcefield(softcore<2,3>{eps, sigma})
+   (SIM/stage_anatelophase/simulation_driver.cpp:77-91). */
+int gc_add_pair_softcore(gc_ctx *ctx, double eps, double sigma);
+/* apply_cutoff(softwell<6>) on set_neighbor_targets(targets)
+   (SIM/stage_interphase/simulation_driver_forcefield.cpp:162-185). */
+int gc_add_pair_softwell(gc_ctx *ctx, double eps, double decay, double cutoff,
+                         int32_t n_targets, const int32_t *targets);
+/* make_bonded_pairwise_forcefield + add_bonded_pair/add_bonded_range
+   (MD/forcefield/bonded_pairwise_forcefield.hpp:35-132); pairs = [n][2]. */
+int gc_add_bonds(gc_ctx *ctx, const gc_bond_params *params, int32_t n,
+                 const int32_t *pairs);
+/* make_bonded_triplewise_forcefield(cosine_bending_potential)
+   (MD/forcefield/bonded_triplewise_forcefield.hpp:35-149); triples = [n][3]. */
+int gc_add_triples(gc_ctx *ctx, double bending_energy, int32_t n, const int32_t *triples);
+/* make_ellipsoid_inward_forcefield + make_ellipsoid_outward_forcefield. */
+int gc_set_wall(gc_ctx *ctx, const gc_wall_params *params);
+/* make_point_source_forcefield(pot).set_point_source(pt), all beads. */
+int gc_add_point_source(gc_ctx *ctx, int32_t kind, const double point[3], double p0,
+                        double p1);
+/* kinetochore_fiber_forcefield
+   (SIM/common/forcefield/kinetochore_fiber_forcefield.cpp:8-84):
+   spring K[k] = decay_rate / mobility, rest length[k], bead[k] -> pole. */
+int gc_add_kfiber(gc_ctx *ctx, const double pole[3], int32_t n, const int32_t *beads,
+                  const double *spring, const double *length);
+/* system.add_forcefield / remove_forcefield at run time
+   (SIM/stage_anatelophase/simulation_driver.cpp:244,277-285). */
+int gc_set_term_enabled(gc_ctx *ctx, int32_t term, int32_t enabled);
+
+/* ---- schedule / context ------------------------------------------------ */
+
+int gc_set_schedule(gc_ctx *ctx, const gc_schedule *schedule);
+/* replica = -1 on set applies to all. Only time, semiaxes, core_scale,
+   bond_scale and contact_distance are taken from `in`. */
+int gc_set_context(gc_ctx *ctx, int32_t replica, const gc_context *in);
+int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out);
+
+/* ---- dynamics ---------------------------------------------------------- */
+
+/* md::simulate_brownian_dynamics incl. the per-step driver callback body
+   (schedule, wall ODE, contact-map cadence) executed on device. */
+int gc_run(gc_ctx *ctx, const gc_run_config *config);
+/* Cell-list skin as a fraction of the pair cutoff (0 = rebuild every step). */
+int gc_set_skin(gc_ctx *ctx, double skin_fraction);
+/* Standard normals the device would draw for `step` (1-based) of replica:
+   out = [n_beads][3] floats.  Diagnostic for the Philox stream. */
+int gc_debug_noise(gc_ctx *ctx, int32_t replica, int64_t step, float *out);
+
+/* md::system::compute_force (MD/system.hpp:264-272); out = [n_beads][3].
+   Also refreshes the wall statistics returned by gc_get_context. */
+int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out);
+/* md::system::compute_potential_energy (MD/system.hpp:249-252). */
+int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out);
+
+/* md::neighbor_searcher<open_box>(box, radius).set_points().search()
+   (MD/misc/neighbor_searcher.hpp:22-131): unique pairs i < j with
+   |xi - xj|^2 <= radius^2 (inclusive), sorted by (i, j); pairs = [cap][2]. */
+int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pairs,
+                      size_t capacity, size_t *count);
+
+/* ---- contact map (SIM/stage_interphase/contact_map.cpp:12-85) ---------- */
+
+/* interval = update cadence in steps inside gc_run (0 = never automatic);
+   distance scales with core_scale(t) when scale_by_core is set (interphase
+   callback: contact distance = contactmap_distance * core_scale);
+   table_capacity = hash slots per replica (0 = default). */
+int gc_set_contact_map(gc_ctx *ctx, double distance, int64_t interval,
+                       int32_t scale_by_core, size_t table_capacity);
+/* contact_map::update on the current positions of every replica. */
+int gc_contacts_update(gc_ctx *ctx);
+/* contact_map::accumulate: (i, j, count) sorted by (i, j); replica = -1 sums
+   over replicas.  ijv = [cap][3]; *count receives the number of triples even
+   when it exceeds capacity (then GC_ERR_CAPACITY). ijv may be NULL to query. */
+int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity,
+                      size_t *count);
+int gc_contacts_clear(gc_ctx *ctx);
+
+/* ---- observables ------------------------------------------------------- */
+
+/* Squared radius of gyration per chain range [start, end) (harness-defined
+   observable): out = [n_ranges]. */
+int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
+                          const int32_t *ranges, double *out_rg2);
+
+/* Number of kernels launched by this context since creation (bench claim). */
+int gc_launch_count(gc_ctx *ctx, int64_t *out);
+/* Block until all queued device work of the context has finished. */
+int gc_synchronize(gc_ctx *ctx);
+/* CUDA stream handle (cudaStream_t as void*) for event timing by the caller. */
+int gc_stream(gc_ctx *ctx, void **out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GC_B200_H */
