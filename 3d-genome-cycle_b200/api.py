@@ -1,0 +1,349 @@
+"""ctypes binding of the C-ABI in include/gc_b200.h.
+
+The product path is libgc_b200.so (CUDA, sm_100a).  There is no CPU fallback:
+if the library is missing or no GPU is present this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "libgc_b200.so"
+
+GC_BOND_SEMISPRING, GC_BOND_HARMONIC, GC_BOND_SPRING = 0, 1, 2
+GC_SOURCE_SEMISPRING, GC_SOURCE_FORCE_FLUX = 0, 1
+GC_MASK_ALL = 0xFFFFFFFF
+
+
+class BondParams(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("mix_ab", C.c_int32), ("scale", C.c_int32),
+                ("reserved", C.c_int32), ("K_a", C.c_double), ("K_b", C.c_double),
+                ("l_a", C.c_double), ("l_b", C.c_double)]
+
+
+class WallParams(C.Structure):
+    _fields_ = [("semiaxes", C.c_double * 3), ("eps_a", C.c_double), ("sigma_a", C.c_double),
+                ("eps_b", C.c_double), ("sigma_b", C.c_double), ("wall_a", C.c_double),
+                ("wall_b", C.c_double), ("outward_spring", C.c_double),
+                ("scale_by_core", C.c_int32), ("ode_enabled", C.c_int32),
+                ("ode_mobility", C.c_double), ("ode_spring", C.c_double * 3)]
+
+
+class Schedule(C.Structure):
+    _fields_ = [("enabled", C.c_int32), ("reserved", C.c_int32), ("core_init", C.c_double),
+                ("core_tau", C.c_double), ("bond_init", C.c_double), ("bond_tau", C.c_double)]
+
+
+class Context(C.Structure):
+    _fields_ = [("time", C.c_double), ("semiaxes", C.c_double * 3), ("core_scale", C.c_double),
+                ("bond_scale", C.c_double), ("contact_distance", C.c_double),
+                ("axial_reaction", C.c_double * 3), ("reaction_force", C.c_double),
+                ("last_timestep", C.c_double), ("step", C.c_int64), ("rebuilds", C.c_int64)]
+
+    def as_dict(self):
+        return dict(time=self.time, semiaxes=list(self.semiaxes), core_scale=self.core_scale,
+                    bond_scale=self.bond_scale, contact_distance=self.contact_distance,
+                    axial_reaction=list(self.axial_reaction), reaction_force=self.reaction_force,
+                    last_timestep=self.last_timestep, step=self.step, rebuilds=self.rebuilds)
+
+
+class RunConfig(C.Structure):
+    _fields_ = [("steps", C.c_int64), ("temperature", C.c_double), ("timestep", C.c_double),
+                ("spacestep", C.c_double), ("restart", C.c_int32), ("reserved", C.c_int32),
+                ("noise", C.POINTER(C.c_double))]
+
+
+# every symbol include/gc_b200.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+SYMBOLS = [
+    ("gc_create", C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P)]),
+    ("gc_destroy", C.c_int, [_P]),
+    ("gc_last_error", C.c_char_p, [_P]),
+    ("gc_version", C.c_char_p, []),
+    ("gc_set_bead_attrs", C.c_int, [_P, _dp, _dp, _dp]),
+    ("gc_set_positions", C.c_int, [_P, C.c_int32, _dp]),
+    ("gc_get_positions", C.c_int, [_P, C.c_int32, _dp]),
+    ("gc_set_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
+    ("gc_get_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
+    ("gc_set_seeds", C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    ("gc_add_pair_softcore_ab", C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32]),
+    ("gc_add_pair_softcore", C.c_int, [_P, C.c_double, C.c_double]),
+    ("gc_add_pair_softwell", C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_int32, _ip]),
+    ("gc_add_bonds", C.c_int, [_P, C.POINTER(BondParams), C.c_int32, _ip]),
+    ("gc_add_triples", C.c_int, [_P, C.c_double, C.c_int32, _ip]),
+    ("gc_set_wall", C.c_int, [_P, C.POINTER(WallParams)]),
+    ("gc_add_point_source", C.c_int, [_P, C.c_int32, _dp, C.c_double, C.c_double]),
+    ("gc_add_kfiber", C.c_int, [_P, _dp, C.c_int32, _ip, _dp, _dp]),
+    ("gc_set_term_enabled", C.c_int, [_P, C.c_int32, C.c_int32]),
+    ("gc_set_schedule", C.c_int, [_P, C.POINTER(Schedule)]),
+    ("gc_set_context", C.c_int, [_P, C.c_int32, C.POINTER(Context)]),
+    ("gc_get_context", C.c_int, [_P, C.c_int32, C.POINTER(Context)]),
+    ("gc_run", C.c_int, [_P, C.POINTER(RunConfig)]),
+    ("gc_set_skin", C.c_int, [_P, C.c_double]),
+    ("gc_debug_noise", C.c_int, [_P, C.c_int32, C.c_int64, C.POINTER(C.c_float)]),
+    ("gc_compute_force", C.c_int, [_P, C.c_int32, C.c_uint32, _dp]),
+    ("gc_compute_energy", C.c_int, [_P, C.c_int32, C.c_uint32, _dp]),
+    ("gc_neighbor_pairs", C.c_int, [_P, C.c_int32, C.c_double, C.POINTER(C.c_uint32), C.c_size_t,
+                                    C.POINTER(C.c_size_t)]),
+    ("gc_set_contact_map", C.c_int, [_P, C.c_double, C.c_int64, C.c_int32, C.c_size_t]),
+    ("gc_contacts_update", C.c_int, [_P]),
+    ("gc_contacts_fetch", C.c_int, [_P, C.c_int32, C.POINTER(C.c_uint32), C.c_size_t,
+                                    C.POINTER(C.c_size_t)]),
+    ("gc_contacts_clear", C.c_int, [_P]),
+    ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
+    ("gc_launch_count", C.c_int, [_P, C.POINTER(C.c_int64)]),
+    ("gc_synchronize", C.c_int, [_P]),
+    ("gc_stream", C.c_int, [_P, C.POINTER(C.c_void_p)]),
+]
+
+_lib = None
+
+
+def load_library(path: os.PathLike | None = None) -> C.CDLL:
+    """Loads libgc_b200.so and types every exported symbol.  Raises if absent."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise RuntimeError(f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)")
+    lib = C.CDLL(str(p))
+    for name, res, args in SYMBOLS:
+        fn = getattr(lib, name)   # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+class GcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"gc_b200 error {code}: {message}")
+        self.code = code
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _ptr(a, typ):
+    return a.ctypes.data_as(C.POINTER(typ))
+
+
+class System:
+    """R replicas of an N-bead system on one GPU (thin wrapper over gc_ctx)."""
+
+    def __init__(self, n_beads: int, n_replicas: int = 1, device: int = 0):
+        self.lib = load_library()
+        self.n = int(n_beads)
+        self.n_rep = int(n_replicas)
+        self._h = _P()
+        rc = self.lib.gc_create(self.n, self.n_rep, int(device), C.byref(self._h))
+        if rc != 0:
+            msg = self.lib.gc_last_error(self._h).decode() if self._h else "no CUDA device"
+            raise GcError(rc, msg)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.gc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise GcError(rc, self.lib.gc_last_error(self._h).decode())
+        return rc
+
+    # ---- beads -----------------------------------------------------------
+    def set_bead_attrs(self, mobility, a=None, b=None):
+        m = _d(mobility)
+        aa = _d(a) if a is not None else None
+        bb = _d(b) if b is not None else None
+        self._ck(self.lib.gc_set_bead_attrs(self._h, _ptr(m, C.c_double),
+                                            _ptr(aa, C.c_double) if aa is not None else None,
+                                            _ptr(bb, C.c_double) if bb is not None else None))
+
+    def set_positions(self, xyz, replica=-1):
+        x = _d(xyz).reshape(self.n, 3)
+        self._ck(self.lib.gc_set_positions(self._h, replica, _ptr(x, C.c_double)))
+
+    def get_positions(self, replica=0):
+        x = np.empty((self.n, 3), dtype=np.float64)
+        self._ck(self.lib.gc_get_positions(self._h, replica, _ptr(x, C.c_double)))
+        return x
+
+    def set_positions_f32(self, xyz, replica=-1):
+        x = np.ascontiguousarray(xyz, dtype=np.float32).reshape(self.n, 3)
+        self._ck(self.lib.gc_set_positions_f32(self._h, replica, _ptr(x, C.c_float)))
+
+    def get_positions_f32(self, replica=0):
+        x = np.empty((self.n, 3), dtype=np.float32)
+        self._ck(self.lib.gc_get_positions_f32(self._h, replica, _ptr(x, C.c_float)))
+        return x
+
+    def set_seeds(self, seeds):
+        s = np.ascontiguousarray(seeds, dtype=np.uint64)
+        assert s.size == self.n_rep
+        self._ck(self.lib.gc_set_seeds(self._h, _ptr(s, C.c_uint64)))
+
+    # ---- terms -----------------------------------------------------------
+    def add_pair_softcore_ab(self, eps_a, sigma_a, eps_b, sigma_b, scale_by_core=True):
+        return self._ck(self.lib.gc_add_pair_softcore_ab(self._h, eps_a, sigma_a, eps_b, sigma_b,
+                                                         int(scale_by_core)))
+
+    def add_pair_softcore(self, eps, sigma):
+        return self._ck(self.lib.gc_add_pair_softcore(self._h, eps, sigma))
+
+    def add_pair_softwell(self, eps, decay, cutoff, targets):
+        t = _i(targets)
+        return self._ck(self.lib.gc_add_pair_softwell(self._h, eps, decay, cutoff, t.size,
+                                                      _ptr(t, C.c_int32)))
+
+    def add_bonds(self, pairs, kind=GC_BOND_SEMISPRING, K_a=1.0, K_b=0.0, l_a=0.0, l_b=0.0,
+                  mix_ab=False, scale=False):
+        p = _i(pairs).reshape(-1, 2)
+        bp = BondParams(kind, int(mix_ab), int(scale), 0, K_a, K_b, l_a, l_b)
+        return self._ck(self.lib.gc_add_bonds(self._h, C.byref(bp), p.shape[0], _ptr(p, C.c_int32)))
+
+    def add_triples(self, triples, bending_energy):
+        t = _i(triples).reshape(-1, 3)
+        return self._ck(self.lib.gc_add_triples(self._h, bending_energy, t.shape[0],
+                                                _ptr(t, C.c_int32)))
+
+    def set_wall(self, semiaxes, eps_a, sigma_a, eps_b, sigma_b, wall_a, wall_b, outward_spring,
+                 scale_by_core=True, ode_enabled=False, ode_mobility=0.0, ode_spring=(0, 0, 0)):
+        w = WallParams((C.c_double * 3)(*semiaxes), eps_a, sigma_a, eps_b, sigma_b, wall_a, wall_b,
+                       outward_spring, int(scale_by_core), int(ode_enabled), ode_mobility,
+                       (C.c_double * 3)(*ode_spring))
+        return self._ck(self.lib.gc_set_wall(self._h, C.byref(w)))
+
+    def add_point_source(self, kind, point, p0, p1):
+        pt = _d(point)
+        return self._ck(self.lib.gc_add_point_source(self._h, kind, _ptr(pt, C.c_double), p0, p1))
+
+    def add_kfiber(self, pole, beads, spring, length):
+        pl, bd, sp, ln = _d(pole), _i(beads), _d(spring), _d(length)
+        return self._ck(self.lib.gc_add_kfiber(self._h, _ptr(pl, C.c_double), bd.size,
+                                               _ptr(bd, C.c_int32), _ptr(sp, C.c_double),
+                                               _ptr(ln, C.c_double)))
+
+    def set_term_enabled(self, term, enabled):
+        self._ck(self.lib.gc_set_term_enabled(self._h, term, int(enabled)))
+
+    # ---- schedule / context ------------------------------------------------
+    def set_schedule(self, core_init, core_tau, bond_init, bond_tau, enabled=True):
+        s = Schedule(int(enabled), 0, core_init, core_tau, bond_init, bond_tau)
+        self._ck(self.lib.gc_set_schedule(self._h, C.byref(s)))
+
+    def get_context(self, replica=0) -> Context:
+        c = Context()
+        self._ck(self.lib.gc_get_context(self._h, replica, C.byref(c)))
+        return c
+
+    def set_context(self, replica=-1, **kw):
+        c = self.get_context(max(replica, 0))
+        for k, v in kw.items():
+            if k == "semiaxes":
+                c.semiaxes = (C.c_double * 3)(*v)
+            else:
+                setattr(c, k, v)
+        self._ck(self.lib.gc_set_context(self._h, replica, C.byref(c)))
+
+    def set_skin(self, frac):
+        self._ck(self.lib.gc_set_skin(self._h, float(frac)))
+
+    # ---- dynamics ----------------------------------------------------------
+    def run(self, steps, timestep, temperature=1.0, spacestep=0.0, restart=True, noise=None):
+        cfg = RunConfig(int(steps), temperature, timestep, spacestep, int(restart), 0, None)
+        keep = None
+        if noise is not None:
+            keep = _d(noise)
+            assert keep.size == self.n_rep * steps * self.n * 3
+            cfg.noise = _ptr(keep, C.c_double)
+        self._ck(self.lib.gc_run(self._h, C.byref(cfg)))
+
+    def debug_noise(self, step, replica=0):
+        out = np.empty((self.n, 3), dtype=np.float32)
+        self._ck(self.lib.gc_debug_noise(self._h, replica, step, _ptr(out, C.c_float)))
+        return out
+
+    def compute_force(self, mask=GC_MASK_ALL, replica=0):
+        f = np.empty((self.n, 3), dtype=np.float64)
+        self._ck(self.lib.gc_compute_force(self._h, replica, mask, _ptr(f, C.c_double)))
+        return f
+
+    def compute_energy(self, mask=GC_MASK_ALL, replica=0):
+        e = C.c_double()
+        self._ck(self.lib.gc_compute_energy(self._h, replica, mask, C.byref(e)))
+        return e.value
+
+    def neighbor_pairs(self, radius, replica=0, capacity=None):
+        cap = capacity or max(64 * self.n, 1024)
+        while True:
+            out = np.empty((cap, 2), dtype=np.uint32)
+            cnt = C.c_size_t()
+            rc = self.lib.gc_neighbor_pairs(self._h, replica, radius, _ptr(out, C.c_uint32), cap,
+                                            C.byref(cnt))
+            if rc == -5 and capacity is None:
+                cap = cnt.value
+                continue
+            self._ck(rc)
+            return out[:cnt.value].copy()
+
+    # ---- contacts ----------------------------------------------------------
+    def set_contact_map(self, distance, interval=0, scale_by_core=False, table_capacity=0):
+        self._ck(self.lib.gc_set_contact_map(self._h, distance, interval, int(scale_by_core),
+                                             table_capacity))
+
+    def contacts_update(self):
+        self._ck(self.lib.gc_contacts_update(self._h))
+
+    def contacts_fetch(self, replica=0):
+        cnt = C.c_size_t()
+        self._ck(self.lib.gc_contacts_fetch(self._h, replica, None, 0, C.byref(cnt)))
+        out = np.empty((cnt.value, 3), dtype=np.uint32)
+        if cnt.value:
+            self._ck(self.lib.gc_contacts_fetch(self._h, replica, _ptr(out, C.c_uint32), cnt.value,
+                                                C.byref(cnt)))
+        return out
+
+    def contacts_clear(self):
+        self._ck(self.lib.gc_contacts_clear(self._h))
+
+    # ---- observables / misc -----------------------------------------------
+    def radius_of_gyration2(self, ranges, replica=0):
+        r = _i(ranges).reshape(-1, 2)
+        out = np.empty(r.shape[0], dtype=np.float64)
+        self._ck(self.lib.gc_radius_of_gyration(self._h, replica, r.shape[0], _ptr(r, C.c_int32),
+                                                _ptr(out, C.c_double)))
+        return out
+
+    def launch_count(self):
+        v = C.c_int64()
+        self._ck(self.lib.gc_launch_count(self._h, C.byref(v)))
+        return v.value
+
+    def synchronize(self):
+        self._ck(self.lib.gc_synchronize(self._h))
+
+    def stream(self):
+        v = C.c_void_p()
+        self._ck(self.lib.gc_stream(self._h, C.byref(v)))
+        return v.value
