@@ -98,12 +98,18 @@ size_t gco_reference_normals(uint64_t seed, size_t n, double *out);
 /* single-potential probes for the known-answer tests:
    kind: 0 softcore<2,3> 1 softcore<8,3> 2 softwell<6> 3 semispring 4 harmonic
          5 spring 6 force_flux 7 softwell<6>+cutoff(p2)
+         8 softcore<P,Q> with P = (int) p2 / 10, Q = (int) p2 % 10 (the (P,Q)
+           pairs of MDT/potential/test_softcore_potential.cc:55-76)
    returns energy; force written to f[3] */
 double gco_potential_probe(int32_t kind, double p0, double p1, double p2, const double r[3],
                            double f[3]);
 /* cosine bending: forces on i, j, k written to f[9]; returns energy */
 double gco_bending_probe(double bending_energy, const double rij[3], const double rjk[3],
                          double f[9]);
+
+/* detail::evaluate_point (MD/forcefield/ellipsoid_surface_forcefield.hpp:55-90):
+   out = {undefined, delta xyz, strain xyz, implicit} */
+void gco_ellipsoid_probe(const double semiaxes[3], const double pt[3], double out[8]);
 
 #ifdef __cplusplus
 }

@@ -110,6 +110,7 @@ def load(kind="reference"):
         "gco_reference_normals": (C.c_size_t, [C.c_uint64, C.c_size_t, dp]),
         "gco_potential_probe": (C.c_double, [C.c_int32, C.c_double, C.c_double, C.c_double, dp, dp]),
         "gco_bending_probe": (C.c_double, [C.c_double, dp, dp, dp]),
+        "gco_ellipsoid_probe": (None, [dp, dp, dp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -331,3 +332,11 @@ def bending_probe(e0, rij, rjk, kind="reference"):
     e = load(kind).gco_bending_probe(e0, _ptr(a, C.c_double), _ptr(b, C.c_double),
                                      _ptr(f, C.c_double))
     return e, f.reshape(3, 3)
+
+
+def ellipsoid_probe(semiaxes, pt, kind="reference"):
+    a, b = _d(semiaxes), _d(pt)
+    out = np.zeros(8)
+    load(kind).gco_ellipsoid_probe(_ptr(a, C.c_double), _ptr(b, C.c_double), _ptr(out, C.c_double))
+    return dict(undefined=bool(out[0]), delta=out[1:4].copy(), strain=out[4:7].copy(),
+                implicit=out[7])

@@ -732,6 +732,18 @@ double gco_potential_probe(int32_t kind, double p0, double p1, double p2, const 
     case 7:
         eval(md::apply_cutoff(md::softwell_potential<6>{.energy = p0, .decay_distance = p1}, p2));
         break;
+    case 8:
+        switch (int(p2)) {
+        case 21: eval(md::softcore_potential<2, 1>{.energy = p0, .diameter = p1}); break;
+        case 22: eval(md::softcore_potential<2, 2>{.energy = p0, .diameter = p1}); break;
+        case 23: eval(md::softcore_potential<2, 3>{.energy = p0, .diameter = p1}); break;
+        case 33: eval(md::softcore_potential<3, 3>{.energy = p0, .diameter = p1}); break;
+        case 44: eval(md::softcore_potential<4, 4>{.energy = p0, .diameter = p1}); break;
+        case 55: eval(md::softcore_potential<5, 5>{.energy = p0, .diameter = p1}); break;
+        case 83: eval(md::softcore_potential<8, 3>{.energy = p0, .diameter = p1}); break;
+        default: break;
+        }
+        break;
     default: break;
     }
     f[0] = fv.x;
@@ -754,6 +766,23 @@ double gco_bending_probe(double bending_energy, const double rij[3], const doubl
         f[3 * k + 2] = fs[k].z;
     }
     return pot.evaluate_energy(a, b);
+}
+
+void gco_ellipsoid_probe(const double semiaxes[3], const double pt[3], double out[8])
+{
+    md::ellipsoid const el{
+        .center = {0, 0, 0},
+        .semiaxis_x = semiaxes[0],
+        .semiaxis_y = semiaxes[1],
+        .semiaxis_z = semiaxes[2],
+    };
+    auto const ev = md::detail::evaluate_point(el, {pt[0], pt[1], pt[2]});
+    for (int k = 0; k < 8; k++) out[k] = 0;
+    out[0] = ev.undefined ? 1 : 0;
+    if (ev.undefined) return;
+    out[1] = ev.delta.x; out[2] = ev.delta.y; out[3] = ev.delta.z;
+    out[4] = ev.strain.x; out[5] = ev.strain.y; out[6] = ev.strain.z;
+    out[7] = ev.implicit;
 }
 
 } // extern "C"

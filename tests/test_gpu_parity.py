@@ -1,0 +1,313 @@
+"""GPU parity tests: the CUDA path through the C-ABI vs the CPU oracle on the
+same seeded inputs.  Bars (BASELINE.json north_star):
+  * neighbor pair sets and contact triples: bit-exact
+  * forces / positions under identical injected noise: <= 1e-5 relative
+    (FP32 device vs FP64 reference); force norm: max_i|dF_i| / max_i|F_i|,
+    position norm: max|dx| / nucleus size (2.0)
+"""
+import numpy as np
+import pytest
+
+import oracle_py as O
+from gcpkg import gc_b200
+from helpers import build_pair, rel_force_err, small_interphase, stages, synth
+
+pytestmark = pytest.mark.gpu
+
+FORCE_TOL = 1e-5
+POS_TOL = 1e-5 * 2.0
+
+
+def gpu(n, r=1):
+    return gc_b200.System(n, r, 0)
+
+
+def oracle(kind):
+    return lambda n: O.OracleSystem(n, kind)
+
+
+# ---------------------------------------------------------------------------
+# neighbor search
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("n,radius,dist", [(100, 0.3, "normal"), (1000, 0.1, "uniform"),
+                                           (5000, 0.15, "normal"), (2, 5.0, "normal"),
+                                           (1, 1.0, "normal")])
+def test_pair_set_exact_random_points(oracle_kind, n, radius, dist):
+    """MDT/misc/test_neighbor_searcher.cc:54-127 shapes; FP32-representable input."""
+    rng = np.random.default_rng(n)
+    x = rng.normal(size=(n, 3)) if dist == "normal" else rng.random((n, 3))
+    x = x.astype(np.float32).astype(np.float64)
+    g, o = gpu(n), O.OracleSystem(n, oracle_kind)
+    for s in (g, o):
+        s.set_bead_attrs(np.ones(n))
+        s.set_positions(x)
+    np.testing.assert_array_equal(g.neighbor_pairs(radius), o.neighbor_pairs(radius))
+
+
+def test_pair_set_exact_interphase_state(oracle_kind):
+    d, cfg, x = small_interphase()
+    g, o = gpu(d.n), O.OracleSystem(d.n, oracle_kind)
+    for s in (g, o):
+        stages.setup_interphase(s, d, cfg)
+        s.set_positions(x)
+    for radius in (0.15, 0.225, 0.12):     # dcut, Verlet radius, contact distance at s = 0.5
+        a, b = g.neighbor_pairs(radius), o.neighbor_pairs(radius)
+        assert len(b) > d.n
+        np.testing.assert_array_equal(a, b)
+
+
+def test_pair_set_borderline_pairs(oracle_kind):
+    """Pairs placed exactly at / one ulp around the cutoff (inclusive <=,
+    MD/misc/neighbor_searcher.hpp:90)."""
+    r = 0.25
+    base = np.array([[0, 0, 0], [r, 0, 0], [0, np.nextafter(np.float32(r), np.float32(1)), 0],
+                     [0, 0, np.nextafter(np.float32(r), np.float32(0))], [3, 3, 3],
+                     [3 + r, 3, 3]], dtype=np.float32).astype(np.float64)
+    g, o = gpu(len(base)), O.OracleSystem(len(base), oracle_kind)
+    for s in (g, o):
+        s.set_bead_attrs(np.ones(len(base)))
+        s.set_positions(base)
+    a, b = g.neighbor_pairs(r), o.neighbor_pairs(r)
+    np.testing.assert_array_equal(a, b)
+    assert [0, 1] in b.tolist() and [0, 2] not in b.tolist() and [0, 3] in b.tolist()
+
+
+# ---------------------------------------------------------------------------
+# forces, energies, wall statistics
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("core,bond,semi", [(0.5, 0.5, (2.0, 2.0, 2.0)),
+                                            (0.73, 0.61, (2.0, 1.8, 2.1)),
+                                            (1.0, 1.0, (2.3, 2.2, 2.4))])
+def test_interphase_forces_per_term(oracle_kind, core, bond, semi):
+    d, cfg, x = small_interphase(scale=0.05, radius=1.3)
+    x = x.copy()
+    x[::53] *= 1.6                      # some beads beyond the wall -> outward branch
+    x = x.astype(np.float32).astype(np.float64)
+    (g, terms), (o, _) = build_pair(gpu, d, cfg, x), build_pair(oracle(oracle_kind), d, cfg, x)
+    for s in (g, o):
+        s.set_context(core_scale=core, bond_scale=bond, semiaxes=semi, contact_distance=0.1)
+    for name, t in terms.items():
+        Fg, Fo = g.compute_force(1 << t), o.compute_force(1 << t)
+        if np.abs(Fo).max() == 0:
+            assert np.abs(Fg).max() == 0, name
+            continue
+        assert rel_force_err(Fg, Fo) < FORCE_TOL, name
+    assert rel_force_err(g.compute_force(), o.compute_force()) < FORCE_TOL
+    cg, co = g.get_context(), o.get_context()
+    scale = max(abs(v) for v in co.axial_reaction)
+    assert scale > 0
+    for k in range(3):
+        assert abs(cg.axial_reaction[k] - co.axial_reaction[k]) < 1e-5 * scale
+    assert cg.reaction_force == pytest.approx(co.reaction_force, rel=1e-5)
+    for name, t in terms.items():
+        Eg, Eo = g.compute_energy(1 << t), o.compute_energy(1 << t)
+        assert Eg == pytest.approx(Eo, rel=2e-5, abs=1e-6), name
+    assert g.compute_energy() == pytest.approx(o.compute_energy(), rel=2e-5)
+
+
+def test_mitotic_forces(oracle_kind):
+    d = synth.make_diploid_design(scale=0.3)
+    mcfg = synth.MitoticConfig(polar_ejection_force=0.7, polar_ejection_cross_section=0.04,
+                               kfiber_length_anaphase=0.2, kfiber_length_prometaphase=0.3,
+                               telophase_bond_spring_multiplier=0.5,
+                               telophase_bending_energy_multiplier=2.0)
+    rng = np.random.default_rng(2)
+    md = synth.make_mitotic_design(d, mcfg)
+    x = (synth.rod_positions(md, mcfg) + rng.normal(size=(md.n, 3)) * 0.05)
+    x = x.astype(np.float32).astype(np.float64)
+    g, o = gpu(md.n), O.OracleSystem(md.n, oracle_kind)
+    for s in (g, o):
+        t = stages.setup_anatelophase(s, md, mcfg)
+        s.set_positions(x)
+    for enter in (stages.enter_anaphase, stages.enter_telophase):
+        enter(g, t), enter(o, t)
+        assert rel_force_err(g.compute_force(), o.compute_force()) < FORCE_TOL
+        assert g.compute_energy() == pytest.approx(o.compute_energy(), rel=2e-5)
+
+    md = synth.make_mitotic_design(d, mcfg, sisters=True)
+    x = (rng.normal(size=(md.n, 3)) * 1.5).astype(np.float32).astype(np.float64)
+    g, o = gpu(md.n), O.OracleSystem(md.n, oracle_kind)
+    for s in (g, o):
+        t = stages.setup_prometaphase(s, md, mcfg)
+        s.set_positions(x)
+    for name, tid in t.items():
+        Fo = o.compute_force(1 << tid)
+        assert rel_force_err(g.compute_force(1 << tid), Fo) < FORCE_TOL, name
+        assert g.compute_energy(1 << tid) == pytest.approx(o.compute_energy(1 << tid), rel=2e-5,
+                                                           abs=1e-6), name
+
+
+# ---------------------------------------------------------------------------
+# trajectories under injected noise
+# ---------------------------------------------------------------------------
+def test_interphase_trajectory_injected_noise(oracle_kind):
+    """100 fused steps: schedule + wall ODE + contact map on device."""
+    d, cfg, x = small_interphase(scale=0.02, radius=0.6)
+    steps = 100
+    z = np.random.default_rng(7).normal(size=(steps, d.n, 3))
+    (g, _), (o, _) = build_pair(gpu, d, cfg, x), build_pair(oracle(oracle_kind), d, cfg, x)
+    for s in (g, o):
+        stages.interphase_callback0(s, cfg)
+    g.run(steps, cfg.timestep, noise=z)
+    out = o.run(steps, cfg.timestep, noise=z, interphase_callback=True, want_ctx=True)
+    assert np.abs(g.get_positions() - o.get_positions()).max() < POS_TOL
+    cg, co = g.get_context(), o.get_context()
+    assert cg.step == steps
+    assert cg.time == pytest.approx(co.time, rel=1e-12)
+    assert cg.core_scale == pytest.approx(co.core_scale, rel=1e-12)
+    assert cg.bond_scale == pytest.approx(co.bond_scale, rel=1e-12)
+    np.testing.assert_allclose(list(cg.semiaxes), list(co.semiaxes), rtol=1e-7)
+    assert abs(co.semiaxes[0] - cfg.wall_semiaxes_init[0]) > 1e-4       # the wall did move
+    # contact maps: same pairs except where a pair sits within FP32 noise of
+    # the contact distance after 100 steps
+    a = {(i, j): v for i, j, v in g.contacts_fetch().tolist()}
+    b = {(i, j): v for i, j, v in o.contacts_fetch().tolist()}
+    assert len(b) > 0
+    diff = sum(abs(a.get(k, 0) - b.get(k, 0)) for k in set(a) | set(b))
+    assert diff <= max(2, int(2e-3 * sum(b.values())))
+
+
+def test_relaxation_adaptive_timestep(oracle_kind):
+    d, cfg, x = small_interphase(scale=0.02, radius=0.6)
+    steps = 30
+    z = np.random.default_rng(8).normal(size=(steps, d.n, 3))
+    (g, _), (o, _) = build_pair(gpu, d, cfg, x), build_pair(oracle(oracle_kind), d, cfg, x)
+    g.run(steps, cfg.timestep, spacestep=cfg.relaxation_spacestep, noise=z)
+    out = o.run(steps, cfg.timestep, spacestep=cfg.relaxation_spacestep, noise=z, want_ctx=True)
+    assert np.abs(g.get_positions() - o.get_positions()).max() < POS_TOL
+    assert g.get_context().last_timestep == pytest.approx(out["ctx"][-1, 6], rel=1e-4)
+    assert out["ctx"][-1, 6] < cfg.timestep
+
+
+def test_anatelophase_trajectory(oracle_kind):
+    d = synth.make_diploid_design(scale=0.3)
+    mcfg = synth.MitoticConfig()
+    md = synth.make_mitotic_design(d, mcfg)
+    x = synth.rod_positions(md, mcfg)
+    g, o = gpu(md.n), O.OracleSystem(md.n, oracle_kind)
+    for s in (g, o):
+        t = stages.setup_anatelophase(s, md, mcfg)
+        s.set_positions(x)
+    rng = np.random.default_rng(3)
+    for enter, steps in ((stages.enter_anaphase, 60), (stages.enter_telophase, 40)):
+        enter(g, t), enter(o, t)
+        z = rng.normal(size=(steps, md.n, 3))
+        g.run(steps, mcfg.timestep, noise=z)
+        o.run(steps, mcfg.timestep, noise=z)
+        assert np.abs(g.get_positions() - o.get_positions()).max() < 1e-5 * 5.0
+
+
+def test_contact_update_exact(oracle_kind):
+    d, cfg, x = small_interphase()
+    (g, _), (o, _) = build_pair(gpu, d, cfg, x), build_pair(oracle(oracle_kind), d, cfg, x)
+    for s in (g, o):
+        s.set_context(contact_distance=0.12)
+        s.contacts_update()
+        s.contacts_update()
+    a, b = g.contacts_fetch(), o.contacts_fetch()
+    assert len(b) > d.n and (b[:, 2] == 2).all()
+    np.testing.assert_array_equal(a, b)
+    g.contacts_clear()
+    assert len(g.contacts_fetch()) == 0
+
+
+# ---------------------------------------------------------------------------
+# replicas, skin, determinism, Philox
+# ---------------------------------------------------------------------------
+def test_replicas_are_independent_and_consistent(oracle_kind):
+    d, cfg, x = small_interphase(scale=0.02, radius=0.6)
+    R, steps = 3, 20
+    z = np.random.default_rng(9).normal(size=(R, steps, d.n, 3))
+    g = gpu(d.n, R)
+    stages.setup_interphase(g, d, cfg)
+    g.set_positions(x)
+    stages.interphase_callback0(g, cfg)
+    g.run(steps, cfg.timestep, noise=z)
+    for r in range(R):
+        o, _ = build_pair(oracle(oracle_kind), d, cfg, x)
+        stages.interphase_callback0(o, cfg)
+        o.run(steps, cfg.timestep, noise=z[r], interphase_callback=True)
+        assert np.abs(g.get_positions(r) - o.get_positions()).max() < POS_TOL
+
+
+@pytest.mark.parametrize("skin", [0.0, 0.2, 0.5])
+def test_skin_does_not_change_results(skin):
+    d, cfg, x = small_interphase(scale=0.02, radius=0.6)
+    steps = 60
+    z = np.random.default_rng(10).normal(size=(steps, d.n, 3))
+    res = []
+    for s_ in (0.0, skin):
+        g, _ = build_pair(gpu, d, cfg, x)
+        g.set_skin(s_)
+        stages.interphase_callback0(g, cfg)
+        g.run(steps, cfg.timestep, noise=z)
+        res.append((g.get_positions(), g.get_context().rebuilds))
+    assert np.abs(res[0][0] - res[1][0]).max() < 1e-6
+    if skin >= 0.5:
+        assert res[1][1] < res[0][1]
+
+
+def test_run_is_deterministic_and_chunkable():
+    d, cfg, x = small_interphase(scale=0.02, radius=0.6)
+    out = []
+    for chunks in ((40,), (40,), (10, 25, 5)):
+        g, _ = build_pair(gpu, d, cfg, x)
+        g.set_seeds([1234])
+        stages.interphase_callback0(g, cfg)
+        first = True
+        for c in chunks:
+            g.run(c, cfg.timestep, restart=first)
+            first = False
+        out.append((g.get_positions_f32(), g.contacts_fetch()))
+    assert np.array_equal(out[0][0], out[1][0])          # bit-reproducible
+    assert np.array_equal(out[0][0], out[2][0])          # chunking changes nothing
+    assert np.array_equal(out[0][1], out[2][1])
+
+
+def test_philox_stream_is_standard_normal():
+    n = 200000
+    g = gpu(n)
+    g.set_bead_attrs(np.ones(n))
+    g.set_seeds([42])
+    z1, z2 = g.debug_noise(1), g.debug_noise(2)
+    assert not np.array_equal(z1, z2)
+    z = np.concatenate([z1.ravel(), z2.ravel()]).astype(np.float64)
+    assert abs(z.mean()) < 5e-3 and abs(z.std() - 1) < 5e-3
+    assert abs((z ** 3).mean()) < 2e-2 and abs((z ** 4).mean() - 3) < 5e-2
+    from scipy import stats
+    assert stats.kstest(z[:100000], "norm").pvalue > 1e-3
+    # components are uncorrelated
+    c = np.corrcoef(z1.T.astype(np.float64))
+    assert np.abs(c - np.eye(3)).max() < 1e-2
+
+
+def test_brownian_free_diffusion_statistics():
+    """Free particles: <dx^2> per axis = 2 kT mu t  (BAOAB-limit averaging of
+    consecutive noises keeps the long-time diffusion constant)."""
+    n, steps, dt, mu = 100000, 50, 1e-3, 0.7
+    g = gpu(n)
+    g.set_bead_attrs(np.full(n, mu))
+    x0 = np.zeros((n, 3))
+    g.set_positions(x0)
+    g.set_seeds([7])
+    g.run(steps, dt)
+    x = g.get_positions()
+    # x_n = W_n / 2 + sum_{k<n} W_k  =>  variance = (n - 3/4) * 2 kT mu dt
+    want = 2 * mu * dt * (steps - 0.75)
+    assert x.var(axis=0) == pytest.approx(want, rel=0.03)
+    assert np.abs(x.mean(axis=0)).max() < 4 * np.sqrt(want / n)
+
+
+def test_error_reporting():
+    g = gpu(10)
+    with pytest.raises(gc_b200.GcError):
+        g.run(1, 1e-3)                          # attrs not set
+    g.set_bead_attrs(np.ones(10))
+    x = np.zeros((10, 3))
+    x[3, 1] = np.nan
+    g.set_positions(x)
+    with pytest.raises(gc_b200.GcError) as e:
+        g.run(1, 1e-3)
+    assert e.value.code == -4
+    with pytest.raises(gc_b200.GcError):
+        g.add_bonds([[0, 99]])
