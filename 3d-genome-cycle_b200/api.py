@@ -97,6 +97,7 @@ SYMBOLS = [
                                     C.POINTER(C.c_size_t)]),
     ("gc_contacts_clear", C.c_int, [_P]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
+    ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_launch_count", C.c_int, [_P, C.POINTER(C.c_int64)]),
     ("gc_synchronize", C.c_int, [_P]),
     ("gc_stream", C.c_int, [_P, C.POINTER(C.c_void_p)]),
@@ -334,6 +335,13 @@ class System:
         self._ck(self.lib.gc_radius_of_gyration(self._h, replica, r.shape[0], _ptr(r, C.c_int32),
                                                 _ptr(out, C.c_double)))
         return out
+
+    def debug_grid(self, replica=0):
+        out = np.zeros(16)
+        self._ck(self.lib.gc_debug_grid(self._h, replica, _ptr(out, C.c_double)))
+        return dict(dims=out[:3].astype(int).tolist(), ncell=int(out[3]), origin=out[4:7].tolist(),
+                    cell_size=out[7], rc_valid=out[8], max_disp=out[9], need_rebuild=int(out[10]),
+                    parity=int(out[11]), dt_cur=out[12])
 
     def launch_count(self):
         v = C.c_int64()

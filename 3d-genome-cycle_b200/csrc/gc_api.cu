@@ -735,10 +735,11 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     }
     Params &P = ctx->hp;
     const bool adaptive = c->spacestep != 0.0;
-    if (P.kT != (float) c->temperature || P.dt != (float) c->timestep ||
+    if (P.kT != (float) c->temperature || P.dt_cfg != c->timestep ||
         P.spacestep != (float) c->spacestep) {
         P.kT = (float) c->temperature;
         P.dt = (float) c->timestep;
+        P.dt_cfg = c->timestep;
         P.spacestep = (float) c->spacestep;
         ctx->params_dirty = true;
     }
@@ -869,13 +870,19 @@ int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pai
                       size_t capacity, size_t *count)
 {
     GC_CHECK_CTX(ctx);
-    if (!count || replica < 0 || replica >= ctx->n_rep || !(radius > 0)) {
+    if (!count || replica < 0 || replica >= ctx->n_rep || radius == 0 || radius != radius) {
         return fail(ctx, GC_ERR_INVALID, "bad args");
     }
     int rc = finalize(ctx);
     if (rc) return rc;
-    plan_and_rebuild(ctx, radius);
-    launch_rebuild(ctx);
+    if (radius > 0) {
+        plan_and_rebuild(ctx, radius);
+        launch_rebuild(ctx);
+    } else {
+        // diagnostic: enumerate through the cell list as the last step left it
+        // (tests the skin / rebuild invariant); |radius| must be <= rc_valid
+        radius = -radius;
+    }
     uint2 *d_out = nullptr;
     rc = dev_alloc(ctx, &d_out, capacity);
     if (rc) return rc;
@@ -1095,6 +1102,30 @@ int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges, const 
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     dev_free(ctx, d_ranges);
     dev_free(ctx, d_out);
+    return GC_OK;
+}
+
+int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16])
+{
+    GC_CHECK_CTX(ctx);
+    if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    RepState st;
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    GC_CUDA(ctx, cudaMemcpy(&st, ctx->hp.st + replica, sizeof st, cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 16; k++) out[k] = 0;
+    for (int k = 0; k < 3; k++) {
+        out[k] = st.dims[k];
+        out[4 + k] = st.origin[k];
+    }
+    out[3] = st.ncell;
+    out[7] = st.cell_size;
+    out[8] = st.rc_valid;
+    float md2;
+    memcpy(&md2, &st.maxdisp2_bits, 4);
+    out[9] = std::sqrt((double) md2);
+    out[10] = st.need_rebuild;
+    out[11] = st.parity;
+    out[12] = st.sc.dt_cur;
     return GC_OK;
 }
 

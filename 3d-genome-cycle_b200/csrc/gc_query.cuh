@@ -236,12 +236,14 @@ __global__ void __launch_bounds__(BS) k_energy(Params *Pp, int r, unsigned mask_
                                                   : flux_energy(sc.src_p0[k], sc.src_p1[k], r2));
         }
         if (P.wall.term >= 0 && (mask >> P.wall.term & 1u)) {
-            f3 dual = {sc.q[0] * self.x, sc.q[1] * self.y, sc.q[2] * self.z};
-            float dd = dot(dual, dual);
-            if (dd != 0.0f) {
-                float phi = fmaf(dual.x, self.x, fmaf(dual.y, self.y, fmaf(dual.z, self.z, -1.0f)));
-                float kappa = phi / (2.0f * dd);
-                f3 delta = kappa * dual;
+            double wx = self.x, wy = self.y, wz = self.z;
+            double ux = sc.qd[0] * wx, uy = sc.qd[1] * wy, uz = sc.qd[2] * wz;
+            double ddd = ux * ux + uy * uy + uz * uz;
+            if (ddd != 0.0) {
+                double phid = ux * wx + uy * wy + uz * wz - 1.0;
+                double kd = phid / (2.0 * ddd);
+                float phi = (float) phid;
+                f3 delta = {(float) (kd * ux), (float) (kd * uy), (float) (kd * uz)};
                 float d2 = dot(delta, delta);
                 if (phi < 0.0f) {
                     PairCoef wc = {sc.w_kA2, sc.w_kB2, sc.w_cA, sc.w_cB, sc.w_eA, sc.w_eB, 0.0f};

@@ -36,7 +36,10 @@ __device__ inline void refresh_consts(const Params &P, RepState &st)
                                      P.wall.sigma_b * 0.5, s, PAIR_AB);
         c.w_kA2 = wc.kA2; c.w_kB2 = wc.kB2; c.w_cA = wc.cA; c.w_cB = wc.cB;
         c.w_eA = wc.eA; c.w_eB = wc.eB;
-        for (int k = 0; k < 3; k++) c.q[k] = (float) (1.0 / (st.semiaxes[k] * st.semiaxes[k]));
+        for (int k = 0; k < 3; k++) {
+            c.qd[k] = 1.0 / (st.semiaxes[k] * st.semiaxes[k]);
+            c.q[k] = (float) c.qd[k];
+        }
         c.wall_a = (float) P.wall.wall_a;
         c.wall_b = (float) P.wall.wall_b;
         c.wall_K = (float) P.wall.outward_spring;
@@ -201,12 +204,19 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
     // central in delta, so iso = f and aniso = 0 and the reference's
     // iso + (aniso - iso) o strain reduces to f o (1 - strain).
     if (P.wall.term >= 0 && (mask >> P.wall.term & 1u)) {
-        f3 dual = {sc.q[0] * self.x, sc.q[1] * self.y, sc.q[2] * self.z};
-        float dd = dot(dual, dual);
-        if (dd != 0.0f) {
-            float phi = fmaf(dual.x, self.x, fmaf(dual.y, self.y, fmaf(dual.z, self.z, -1.0f)));
-            float kappa = phi / (2.0f * dd);
-            f3 delta = kappa * dual;
+        // The implicit function phi = sum q x^2 - 1 cancels to ~1e-2 near the wall
+        // and the steep softcore<8,3> amplifies its error, so the point
+        // evaluation (evaluate_point, lines 55-90) is done in FP64: ~20 DFMA per
+        // bead-step against several hundred FP32 pair candidates.
+        double wx = self.x, wy = self.y, wz = self.z;
+        double ux = sc.qd[0] * wx, uy = sc.qd[1] * wy, uz = sc.qd[2] * wz;
+        double ddd = ux * ux + uy * uy + uz * uz;
+        if (ddd != 0.0) {
+            double phid = ux * wx + uy * wy + uz * wz - 1.0;
+            double kd = phid / (2.0 * ddd);
+            float phi = (float) phid;
+            float kappa = (float) kd;
+            f3 delta = {(float) (kd * ux), (float) (kd * uy), (float) (kd * uz)};
             float d2 = dot(delta, delta);
             float fac;
             if (phi < 0.0f) {
@@ -357,7 +367,7 @@ __device__ inline void finalize_step(const Params &P, RepState &st, double dt_us
     st.dt_prev = st.dt_last;
     st.dt_last = dt_used;
     st.step += 1;
-    st.time = (double) st.step * (double) P.dt;
+    st.time = (double) st.step * P.dt_cfg;
 
     st.contact_distance_prev = st.contact_distance;
     if (P.sched.enabled) {
@@ -370,7 +380,7 @@ __device__ inline void finalize_step(const Params &P, RepState &st, double dt_us
     if (P.wall.term >= 0 && P.wall.ode_enabled) {
         for (int k = 0; k < 3; k++) {
             double net = st.axial[k] - P.wall.ode_spring[k] * st.semiaxes[k];
-            st.semiaxes[k] += (double) P.dt * P.wall.ode_mobility * net;
+            st.semiaxes[k] += P.dt_cfg * P.wall.ode_mobility * net;
         }
     }
     st.parity ^= 1;
@@ -504,7 +514,7 @@ __global__ void __launch_bounds__(BS) k_step(Params *Pp, unsigned mask_arg, int 
     if (last && threadIdx.x == 0) {
         finalize_stats(st);
         if (MODE == STEP_FUSED) {
-            finalize_step(P, st, (double) P.dt);
+            finalize_step(P, st, P.dt_cfg);
         } else {
             float dtc = P.dt;
             if (P.spacestep != 0.0f) {
@@ -553,6 +563,11 @@ __global__ void k_plan(Params *Pp, double radius_override)
     st.need_rebuild = 1;
     st.maxdisp2_bits = 0u;
     st.rebuilds += 1;
+    // the next step accumulates its own bounding box from scratch
+    for (int k = 0; k < 3; k++) {
+        st.bbox_min[k] = 0x7fffffff;
+        st.bbox_max[k] = (int) 0x80000000;
+    }
     refresh_consts(P, st);
 }
 

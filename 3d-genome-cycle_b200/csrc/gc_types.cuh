@@ -94,6 +94,7 @@ struct TetherEntry { int pole; float spring; float length; int term; };
 // FP32 constants of one step, derived from the FP64 context by the last block
 // of the previous step (refresh_consts) so that no per-bead FP64 work is needed.
 struct StepConst {
+    double qd[3];                                 // 1 / semiaxis^2 (wall geometry is FP64)
     float kA2, kB2, cA, cB, eA, eB, rc2;          // pair soft cores (PairCoef)
     float w_kA2, w_kB2, w_cA, w_cB, w_eA, w_eB;   // wall inward soft cores (half diameters)
     float q[3];                                   // 1 / semiaxis^2
@@ -149,6 +150,7 @@ struct Params {
     float skin;                    // fraction of the cutoff
     float kT;
     float dt;                      // configured dt (dt_max in adaptive mode)
+    double dt_cfg;                 // the same in FP64 (time, wall ODE)
     float spacestep;
     unsigned int enabled;          // term enable bits
 

@@ -219,7 +219,9 @@ int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *
 
 /* md::neighbor_searcher<open_box>(box, radius).set_points().search()
    (MD/misc/neighbor_searcher.hpp:22-131): unique pairs i < j with
-   |xi - xj|^2 <= radius^2 (inclusive), sorted by (i, j); pairs = [cap][2]. */
+   |xi - xj|^2 <= radius^2 (inclusive), sorted by (i, j); pairs = [cap][2].
+   Diagnostic: radius < 0 searches |radius| through the cell list exactly as
+   the last step left it (no re-binning), to test the skin invariant. */
 int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pairs,
                       size_t capacity, size_t *count);
 
@@ -246,6 +248,11 @@ int gc_contacts_clear(gc_ctx *ctx);
    observable): out = [n_ranges]. */
 int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
                           const int32_t *ranges, double *out_rg2);
+
+/* Diagnostic view of the cell list of one replica: out = {dims x,y,z, ncell,
+   origin x,y,z, cell_size, rc_valid, max displacement since rebuild,
+   need_rebuild, parity, dt_cur, 0, 0, 0}. */
+int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16]);
 
 /* Number of kernels launched by this context since creation (bench claim). */
 int gc_launch_count(gc_ctx *ctx, int64_t *out);

@@ -3,6 +3,7 @@ import sys, time
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
+import os
 import numpy as np
 from gcpkg import gc_b200
 synth, stages = gc_b200.synth, gc_b200.stages
@@ -23,11 +24,11 @@ for R in reps:
         g.set_skin(skin)
         g.set_seeds(np.arange(1, R + 1, dtype=np.uint64))
         t0 = time.time()
-        g.run(200, cfg.timestep, spacestep=cfg.relaxation_spacestep)      # relaxation
+        g.run(int(os.environ.get("QB_RELAX", 200)), cfg.timestep, spacestep=cfg.relaxation_spacestep)      # relaxation
         t_relax = time.time() - t0
         stages.interphase_callback0(g, cfg)
-        g.run(100, cfg.timestep)                                          # warm-up
-        steps = 400
+        g.run(int(os.environ.get("QB_WARM", 100)), cfg.timestep)                                          # warm-up
+        steps = int(os.environ.get("QB_STEPS", 400))
         rb0 = g.get_context().rebuilds
         t0 = time.time()
         g.run(steps, cfg.timestep, restart=False)
