@@ -780,19 +780,20 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
 
     const long long interval = P.contact.enabled ? P.contact.interval : 0;
     const dim3 g = bead_grid(ctx, BS);
+    const dim3 gs = bead_grid(ctx, SBEADS);
     for (long long i = 0; i < c->steps; i++) {
         launch_rebuild(ctx);
         // contact update of the driver callback for the step just finished
         // (SIM/stage_interphase/simulation_driver_interphase.cpp:38-40)
         if (interval > 0 && ctx->run_step > 0 && ctx->run_step % interval == 0 && i > 0) {
-            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, g, BS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
                    (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
         }
         if (adaptive) {
-            LAUNCH(ctx, k_step<STEP_FORCE>, g, BS, ctx->dp, 0u, 1);
+            LAUNCH(ctx, k_step<STEP_FORCE>, gs, SBS, ctx->dp, 0u, 1);
             LAUNCH(ctx, k_integrate, g, BS, ctx->dp);
         } else {
-            LAUNCH(ctx, k_step<STEP_FUSED>, g, BS, ctx->dp, 0u, 1);
+            LAUNCH(ctx, k_step<STEP_FUSED>, gs, SBS, ctx->dp, 0u, 1);
         }
         ctx->run_step++;
         ctx->parity ^= 1;
@@ -800,7 +801,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     // the callback of the last step of this chunk
     if (interval > 0 && c->steps > 0 && ctx->run_step % interval == 0) {
         launch_rebuild(ctx);
-        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, g, BS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
                (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
     }
     return check_device_errors(ctx);
@@ -831,7 +832,7 @@ int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *o
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_step<STEP_FORCE>, bead_grid(ctx, BS), BS, ctx->dp, term_mask, 0);
+    LAUNCH(ctx, k_step<STEP_FORCE>, bead_grid(ctx, SBEADS), SBS, ctx->dp, term_mask, 0);
     std::vector<float4> f((size_t) ctx->n);
     GC_CUDA(ctx, cudaMemcpyAsync(f.data(), ctx->hp.force + (size_t) replica * ctx->n,
                                  f.size() * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
@@ -887,7 +888,7 @@ int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pai
     rc = dev_alloc(ctx, &d_out, capacity);
     if (rc) return rc;
     GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
-    LAUNCH(ctx, k_pairs<PAIRS_LIST>, bead_grid(ctx, BS), BS, ctx->dp, radius, (int) RADIUS_ARG,
+    LAUNCH(ctx, k_pairs<PAIRS_LIST>, bead_grid(ctx, SBEADS), SBS, ctx->dp, radius, (int) RADIUS_ARG,
            replica, d_out, (unsigned long long) capacity, ctx->d_counter);
     unsigned long long found = 0;
     GC_CUDA(ctx, cudaMemcpyAsync(&found, ctx->d_counter, sizeof found, cudaMemcpyDeviceToHost,
@@ -956,7 +957,7 @@ int gc_contacts_update(gc_ctx *ctx)
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, BS), BS, ctx->dp, 0.0, (int) RADIUS_CONTACT,
+    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT,
            -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
     return check_device_errors(ctx);
 }

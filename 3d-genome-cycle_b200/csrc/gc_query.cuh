@@ -55,17 +55,18 @@ enum RadiusSel : int { RADIUS_ARG = 0, RADIUS_CONTACT = 1, RADIUS_CONTACT_PREV =
 // test is redone in FP64 on the (exactly representable) FP32 coordinates, so
 // the set equals the FP64 reference's on the same inputs.
 template<int MODE>
-__global__ void __launch_bounds__(BS) k_pairs(Params *Pp, double rc_arg, int radius_sel,
-                                              int replica, uint2 *out,
-                                              unsigned long long out_cap,
-                                              unsigned long long *out_count)
+__global__ void __launch_bounds__(SBS) k_pairs(Params *Pp, double rc_arg, int radius_sel,
+                                               int replica, uint2 *out,
+                                               unsigned long long out_cap,
+                                               unsigned long long *out_count)
 {
+    __shared__ PairWalkSmem s_walk[SWARPS];
     Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     if (replica >= 0 && r != replica) return;
-    const int t = blockIdx.x * BS + threadIdx.x;
-    if (t >= P.n) return;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
     double rc = radius_sel == RADIUS_ARG ? rc_arg
               : radius_sel == RADIUS_CONTACT ? st.contact_distance : st.contact_distance_prev;
     if (!(rc > 0.0)) return;
@@ -73,42 +74,32 @@ __global__ void __launch_bounds__(BS) k_pairs(Params *Pp, double rc_arg, int rad
     const float rc2 = (float) rc2d;
     const float band = 1.0e-4f * rc2;
 
-    const size_t ro = (size_t) r * P.n;
-    const float4 *__restrict__ sp = P.spos[st.parity] + ro;
-    const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
-    const float4 self = sp[t];
+    for (int b = 0; b < SPERWARP; b++) {
+    const int t = blockIdx.x * SBEADS + warp * SPERWARP + b;
+    if (t >= P.n) return;                       // warp-uniform
+    const float4 self = P.spos[st.parity][(size_t) r * P.n + t];
     const int idx = __float_as_int(self.w);
-    const int dx = st.dims[0], dy = st.dims[1], dz = st.dims[2];
-    const int M = P.cells_per_cut;
-    int c = P.scell[ro + t];
-    int cx = c % dx, cy = (c / dx) % dy, cz = c / (dx * dy);
-    int x0 = max(cx - M, 0), x1 = min(cx + M, dx - 1);
-    for (int z = max(cz - M, 0); z <= min(cz + M, dz - 1); z++) {
-        for (int y = max(cy - M, 0); y <= min(cy + M, dy - 1); y++) {
-            int row = dx * (y + dy * z);
-            int lo = start[row + x0], hi = start[row + x1 + 1];
-            for (int j = lo; j < hi; j++) {
-                float4 q = __ldg(&sp[j]);
-                int jdx = __float_as_int(q.w);
-                if (jdx <= idx) continue;
-                float ex = self.x - q.x, ey = self.y - q.y, ez = self.z - q.z;
-                float r2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
-                bool in = r2 <= rc2;
-                if (fabsf(r2 - rc2) <= band) {
-                    double fx = (double) self.x - (double) q.x;
-                    double fy = (double) self.y - (double) q.y;
-                    double fz = (double) self.z - (double) q.z;
-                    in = fx * fx + fy * fy + fz * fz <= rc2d;
-                }
-                if (!in) continue;
-                if (MODE == PAIRS_CONTACT) {
-                    contact_insert(P.contact, r, st, (unsigned) idx, (unsigned) jdx);
-                } else {
-                    unsigned long long k = atomicAdd(out_count, 1ull);
-                    if (k < out_cap) out[k] = make_uint2((unsigned) idx, (unsigned) jdx);
-                }
-            }
+
+    pair_walk<true, true>(P, st, r, t, self, rc2, s_walk[warp], lane, [&](PairHit h) {
+        float r2 = fmaf(h.dx, h.dx, fmaf(h.dy, h.dy, h.dz * h.dz));
+        bool in = r2 <= rc2;
+        if (fabsf(r2 - rc2) <= band) {
+            // FP32 differences of FP32 inputs within a factor 2 are exact; redo
+            // the squares and the comparison in FP64 from the original coordinates
+            float4 q = P.pos[st.parity][(size_t) r * P.n + h.j];
+            double fx = (double) self.x - (double) q.x;
+            double fy = (double) self.y - (double) q.y;
+            double fz = (double) self.z - (double) q.z;
+            in = fx * fx + fy * fy + fz * fz <= rc2d;
         }
+        if (!in) return;
+        if (MODE == PAIRS_CONTACT) {
+            contact_insert(P.contact, r, st, (unsigned) idx, (unsigned) h.j);
+        } else {
+            unsigned long long k = atomicAdd(out_count, 1ull);
+            if (k < out_cap) out[k] = make_uint2((unsigned) idx, (unsigned) h.j);
+        }
+    });
     }
 }
 

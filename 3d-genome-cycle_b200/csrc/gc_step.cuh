@@ -7,6 +7,7 @@
 #pragma once
 
 #include "gc_kernels.cuh"
+#include "gc_pairwalk.cuh"
 
 namespace gc {
 
@@ -76,6 +77,8 @@ struct WallAcc {
     float ax, ay, az, reaction;
 };
 
+// PAIRS = false leaves the nonbonded soft cores to pair_force_group().
+template<bool PAIRS>
 __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, int r, int t,
                                          int idx, float4 self4, float2 abi, unsigned mask,
                                          WallAcc &wacc)
@@ -87,7 +90,7 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
     f3 F = {0.0f, 0.0f, 0.0f};
 
     // ---- nonbonded soft cores over the neighbouring cell rows -------------
-    if (P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u)) {
+    if (PAIRS && P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u)) {
         PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
         const bool plain = P.pair.mode == PAIR_PLAIN;
         const float4 *__restrict__ sp = P.spos[par] + ro;
@@ -482,23 +485,123 @@ __device__ __forceinline__ float solve_timestep(float spacestep, float mu, float
 // ---------------------------------------------------------------------------
 // step kernels
 // ---------------------------------------------------------------------------
-template<int MODE>
-__global__ void __launch_bounds__(BS) k_step(Params *Pp, unsigned mask_arg, int use_enabled)
+constexpr int SBS = 256;                 // threads per block of k_step
+constexpr int SWARPS = SBS / 32;         // warps per block
+constexpr int SBEADS = 32;               // beads per block (= one warp in phase 2)
+constexpr int SPERWARP = SBEADS / SWARPS; // beads each warp walks in phase 1
+static_assert(SBEADS == 32, "phase 2 of k_step is written for exactly one warp");
+
+// Single-warp variant of block_reduce_commit (phase 2 of k_step runs on warp 0).
+__device__ __forceinline__ bool warp_reduce_commit(RepState &st, StepRed &s, bool with_wall,
+                                                   bool with_geom, bool with_dt)
 {
+    const int lane = threadIdx.x & 31;
+    float v[8];
+    for (int k = 0; k < 3; k++) { v[k] = warp_min(s.lo[k]); v[3 + k] = warp_max(s.hi[k]); }
+    v[6] = warp_max(s.disp2 != s.disp2 ? INFINITY : s.disp2);
+    bool nan_disp = __any_sync(0xffffffffu, s.disp2 != s.disp2);
+    v[7] = warp_min(s.dtmin);
+    long long q[4];
+    q[0] = warp_sum(__double2ll_rn((double) s.w.ax * GC_FX_SCALE));
+    q[1] = warp_sum(__double2ll_rn((double) s.w.ay * GC_FX_SCALE));
+    q[2] = warp_sum(__double2ll_rn((double) s.w.az * GC_FX_SCALE));
+    q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
+    bool bad = __any_sync(0xffffffffu, s.bad) || nan_disp;
+    int last = 0;
+    if (lane == 0) {
+        if (with_geom) {
+            for (int k = 0; k < 3; k++) {
+                atomicMin(&st.bbox_min[k], float_to_ordered(v[k]));
+                atomicMax(&st.bbox_max[k], float_to_ordered(v[3 + k]));
+            }
+            atomicMax(&st.maxdisp2_bits, __float_as_uint(v[6]));
+        }
+        if (with_dt) atomicMin(&st.dtmin_bits, __float_as_uint(v[7]));
+        if (with_wall) {
+            for (int k = 0; k < 3; k++) {
+                if (q[k]) atomicAdd((unsigned long long *) &st.axial_fx[k], (unsigned long long) q[k]);
+            }
+            if (q[3]) atomicAdd((unsigned long long *) &st.reaction_fx, (unsigned long long) q[3]);
+        }
+        if (bad) atomicExch(&st.error, 1);
+        __threadfence();
+        unsigned int prev = atomicAdd(&st.ticket, 1u);
+        last = prev == gridDim.x - 1;
+        if (last) __threadfence();
+    }
+    return __shfl_sync(0xffffffffu, last, 0) != 0;
+}
+
+// Phase 1: every warp walks the neighbour cells of SPERWARP beads, one after
+// the other, and evaluates the soft cores on compacted hits.  Phase 2: warp 0
+// owns the block's 32 beads, one lane each: bonded / wall / tether / source
+// terms, noise, update, reductions, and (last block only) the per-step callback.
+template<int MODE>
+__global__ void __launch_bounds__(SBS) k_step(Params *Pp, unsigned mask_arg, int use_enabled)
+{
+    __shared__ PairWalkSmem s_walk[SWARPS];
+    __shared__ float4 s_force[SBEADS];
+
     Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
+    const StepConst &sc = st.sc;
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    const int t = blockIdx.x * BS + threadIdx.x;
+    const size_t ro = (size_t) r * P.n;
+
+    // ---- phase 1 ----------------------------------------------------------
+    {
+        const int lane = threadIdx.x & 31;
+        const int warp = threadIdx.x >> 5;
+        const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
+        const PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
+        const bool plain = P.pair.mode == PAIR_PLAIN;
+        const float2 *__restrict__ sab = P.sab + ro;
+        for (int b = 0; b < SPERWARP; b++) {
+            const int slot = warp * SPERWARP + b;
+            const int t = blockIdx.x * SBEADS + slot;
+            float fx = 0.0f, fy = 0.0f, fz = 0.0f;
+            if (t < P.n && pair_on) {                     // warp-uniform
+                const float4 self4 = P.spos[st.parity][ro + t];
+                const float2 abi = sab[t];
+                pair_walk<false, false>(P, st, r, t, self4, pc.rc2, s_walk[warp], lane,
+                                        [&](PairHit h) {
+                    // the bead itself has d = 0 and contributes exactly 0
+                    float a = 1.0f, bb = 0.0f;
+                    if (!plain) {
+                        float2 abj = __ldg(&sab[h.j]);
+                        a = 0.5f * (abi.x + abj.x);
+                        bb = 0.5f * (abi.y + abj.y);
+                    }
+                    float r2 = fmaf(h.dx, h.dx, fmaf(h.dy, h.dy, h.dz * h.dz));
+                    float fac = pair_force_factor(pc, a, bb, r2);
+                    fx = fmaf(fac, h.dx, fx);
+                    fy = fmaf(fac, h.dy, fy);
+                    fz = fmaf(fac, h.dz, fz);
+                });
+                fx = warp_sum_f(fx);
+                fy = warp_sum_f(fy);
+                fz = warp_sum_f(fz);
+            }
+            if (lane == 0) s_force[slot] = make_float4(fx, fy, fz, 0.0f);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x >= 32) return;
+
+    // ---- phase 2 (warp 0) -------------------------------------------------
+    const int t = blockIdx.x * SBEADS + threadIdx.x;
     StepRed red;
     red_init(red);
-
     if (t < P.n) {
-        const size_t ro = (size_t) r * P.n;
         float4 self4 = P.spos[st.parity][ro + t];
         int idx = __float_as_int(self4.w);
         float2 abi = P.sab[ro + t];
-        f3 F = bead_force(P, st, r, t, idx, self4, abi, mask, red.w);
+        f3 F = bead_force<false>(P, st, r, t, idx, self4, abi, mask, red.w);
+        float4 fp = s_force[threadIdx.x];
+        F.x += fp.x;
+        F.y += fp.y;
+        F.z += fp.z;
         if (MODE == STEP_FORCE) {
             P.force[ro + idx] = make_float4(F.x, F.y, F.z, 0.0f);
             if (P.spacestep != 0.0f) {
@@ -510,7 +613,7 @@ __global__ void __launch_bounds__(BS) k_step(Params *Pp, unsigned mask_arg, int 
         }
     }
 
-    bool last = block_reduce_commit<BS>(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
+    bool last = warp_reduce_commit(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
     if (last && threadIdx.x == 0) {
         finalize_stats(st);
         if (MODE == STEP_FUSED) {
