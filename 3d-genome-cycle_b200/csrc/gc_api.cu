@@ -18,6 +18,7 @@
 
 #include "../../include/gc_b200.h"
 #include "gc_query.cuh"
+#include "gc_tile.cuh"
 
 using namespace gc;
 
@@ -68,6 +69,8 @@ struct gc_ctx {
     long long launches = 0;
     double skin = 0.0;
     int use_graph = 0;
+    int use_tile = 1;           // cell-tile step kernel (0: warp-per-bead walk)
+    int tile_grid_x = 1;        // blocks per replica of the cell-tile kernel
 
     // graph cache for the fixed-dt step sequence
     cudaGraphExec_t graph_exec = nullptr;
@@ -191,6 +194,14 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     }
     P.cells_per_cut = 1;
     if (const char *env = getenv("GC_CELLS_PER_CUT")) P.cells_per_cut = std::max(1, atoi(env));
+    {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        int per_sm = 8;
+        if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
+        ctx->tile_grid_x = std::max(4, (sms * per_sm + n_replicas - 1) / n_replicas);
+        if (const char *env = getenv("GC_KERNEL")) ctx->use_tile = strcmp(env, "walk") != 0;
+    }
     P.skin = 0.0f;
     P.kT = 1.0f;
     P.dt = 1.0f;
@@ -212,6 +223,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     if (!rc) rc = dev_alloc(ctx, &P.members, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_of, RN);
     if (!rc) rc = dev_alloc(ctx, &P.force, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.pforce, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_count, (size_t) n_replicas * P.ncell_max);
     if (!rc) rc = dev_alloc(ctx, &P.cell_start, (size_t) n_replicas * (P.ncell_max + 1));
     if (!rc) rc = dev_alloc(ctx, &P.st, (size_t) n_replicas);
@@ -716,6 +728,22 @@ __global__ void k_restart(Params *Pp, double dt)
     st.dt_prev = dt;
 }
 
+// one force evaluation (+ update when fused) for every replica
+void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
+{
+    if (ctx->use_tile) {
+        dim3 g(ctx->tile_grid_x, ctx->n_rep);
+        LAUNCH(ctx, k_pair_tile, g, TB, ctx->dp, mask, use_enabled);
+        dim3 gf = bead_grid(ctx, BS);
+        if (mode == STEP_FUSED) LAUNCH(ctx, k_finish<STEP_FUSED>, gf, BS, ctx->dp, mask, use_enabled);
+        else LAUNCH(ctx, k_finish<STEP_FORCE>, gf, BS, ctx->dp, mask, use_enabled);
+    } else {
+        dim3 g = bead_grid(ctx, SBEADS);
+        if (mode == STEP_FUSED) LAUNCH(ctx, k_step<STEP_FUSED>, g, SBS, ctx->dp, mask, use_enabled);
+        else LAUNCH(ctx, k_step<STEP_FORCE>, g, SBS, ctx->dp, mask, use_enabled);
+    }
+}
+
 } // namespace
 
 extern "C" {
@@ -790,10 +818,10 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
                    (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
         }
         if (adaptive) {
-            LAUNCH(ctx, k_step<STEP_FORCE>, gs, SBS, ctx->dp, 0u, 1);
+            launch_step(ctx, STEP_FORCE, 0u, 1);
             LAUNCH(ctx, k_integrate, g, BS, ctx->dp);
         } else {
-            LAUNCH(ctx, k_step<STEP_FUSED>, gs, SBS, ctx->dp, 0u, 1);
+            launch_step(ctx, STEP_FUSED, 0u, 1);
         }
         ctx->run_step++;
         ctx->parity ^= 1;
@@ -832,7 +860,7 @@ int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *o
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_step<STEP_FORCE>, bead_grid(ctx, SBEADS), SBS, ctx->dp, term_mask, 0);
+    launch_step(ctx, STEP_FORCE, term_mask, 0);
     std::vector<float4> f((size_t) ctx->n);
     GC_CUDA(ctx, cudaMemcpyAsync(f.data(), ctx->hp.force + (size_t) replica * ctx->n,
                                  f.size() * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));

@@ -92,30 +92,41 @@ __device__ __forceinline__ void pair_walk(const Params &P, const RepState &st, i
     __syncwarp();
 
     // ---- 2. stream, test, compact ----------------------------------------------
-    int head = 0, qn = 0, row = 0;
+    // Hot loop: ~30 instructions per 32 candidates.  The row of a lane's k-th
+    // candidate only moves forward, so (end of current row, slot - k) live in
+    // registers and shared memory is touched once per row change.
+    const float4 *spo = sp;
+    float4 *queue = sm.queue;
+    asm volatile("" : "+l"(spo), "+l"(queue));     // keep both in registers (no rematerialisation)
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int head = 0, qn = 0, row = -1, cur_end = 0, shift = 0;
+    const int last = total - 1;
     for (int base = 0; base < total; base += 32) {
         const int k = base + lane;
-        bool in = false;
-        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k < total) {
-            while (k >= sm.row_off[row + 1]) row++;
-            const int j = sm.row_lo[row] + (k - sm.row_off[row]);
-            float4 q = __ldg(&sp[j]);
-            e.x = self.x - q.x;
-            e.y = self.y - q.y;
-            e.z = self.z - q.z;
-            e.w = BY_INDEX ? q.w : __int_as_float(j);
-            float r2 = fmaf(e.x, e.x, fmaf(e.y, e.y, e.z * e.z));
-            in = EXACT ? (r2 <= lim) : (r2 < lim);
-            if (BY_INDEX) in = in && __float_as_int(q.w) > self_idx;
+        const int kk = min(k, last);                 // tail lanes re-test the last candidate
+        if (kk >= cur_end) {
+            do {
+                row++;
+                cur_end = sm.row_off[row + 1];
+            } while (kk >= cur_end);
+            shift = sm.row_lo[row] - sm.row_off[row];
         }
+        const float4 q = __ldg(spo + (unsigned) (kk + shift));
+        float4 e;
+        e.x = self.x - q.x;
+        e.y = self.y - q.y;
+        e.z = self.z - q.z;
+        e.w = BY_INDEX ? q.w : __int_as_float(kk + shift);
+        const float r2 = fmaf(e.x, e.x, fmaf(e.y, e.y, e.z * e.z));
+        bool in = (EXACT ? (r2 <= lim) : (r2 < lim)) & (k <= last);
+        if (BY_INDEX) in = in & (__float_as_int(q.w) > self_idx);
         const unsigned m = __ballot_sync(0xffffffffu, in);
-        if (in) sm.queue[(head + qn + __popc(m & ((1u << lane) - 1u))) & (PW_Q - 1)] = e;
+        if (in) queue[(head + qn + __popc(m & lt_mask)) & (PW_Q - 1)] = e;
         qn += __popc(m);
         if (qn >= 32) {
             // ---- 3. evaluate 32 hits densely -----------------------------------
             __syncwarp();
-            float4 h = sm.queue[(head + lane) & (PW_Q - 1)];
+            float4 h = queue[(head + lane) & (PW_Q - 1)];
             visit(PairHit{h.x, h.y, h.z, __float_as_int(h.w)});
             __syncwarp();
             head = (head + 32) & (PW_Q - 1);
@@ -124,7 +135,7 @@ __device__ __forceinline__ void pair_walk(const Params &P, const RepState &st, i
     }
     __syncwarp();
     if (lane < qn) {
-        float4 h = sm.queue[(head + lane) & (PW_Q - 1)];
+        float4 h = queue[(head + lane) & (PW_Q - 1)];
         visit(PairHit{h.x, h.y, h.z, __float_as_int(h.w)});
     }
 }

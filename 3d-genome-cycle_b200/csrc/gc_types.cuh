@@ -172,7 +172,8 @@ struct Params {
     int *sidx, *scell, *slot_of;
     float2 *sab;
     int *cell_count, *cell_start, *members, *cell_of;
-    float4 *force;
+    float4 *force;                 // total force, ORIGINAL order (adaptive stepper, gc_compute_force)
+    float4 *pforce;                // nonbonded force, SORTED order (k_pair_tile -> k_finish)
     RepState *st;
     const float *noise;            // injected normals [R][steps][N][3] or null
     long long noise_steps;         // steps covered by `noise`
