@@ -98,6 +98,9 @@ SYMBOLS = [
     ("gc_contacts_clear", C.c_int, [_P]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
+    ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
+    ("gc_profile_read", C.c_int, [_P, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), _dp]),
+    ("gc_measure_fp32_peak", C.c_int, [C.c_int32, _dp]),
     ("gc_launch_count", C.c_int, [_P, C.POINTER(C.c_int64)]),
     ("gc_synchronize", C.c_int, [_P]),
     ("gc_stream", C.c_int, [_P, C.POINTER(C.c_void_p)]),
@@ -123,6 +126,15 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     if path is None:
         _lib = lib
     return lib
+
+
+def measure_fp32_peak(device=0):
+    """Measured FP32 FFMA peak of the device in TFLOP/s."""
+    v = C.c_double()
+    rc = load_library().gc_measure_fp32_peak(int(device), C.byref(v))
+    if rc != 0:
+        raise GcError(rc, "gc_measure_fp32_peak failed")
+    return v.value
 
 
 class GcError(RuntimeError):
@@ -342,6 +354,22 @@ class System:
         return dict(dims=out[:3].astype(int).tolist(), ncell=int(out[3]), origin=out[4:7].tolist(),
                     cell_size=out[7], rc_valid=out[8], max_disp=out[9], need_rebuild=int(out[10]),
                     parity=int(out[11]), dt_cur=out[12])
+
+    def profile_enable(self, enabled=True):
+        self._ck(self.lib.gc_profile_enable(self._h, int(enabled)))
+
+    def profile_read(self):
+        """{kernel name: (launches, total_ms)} recorded since profile_enable(True)."""
+        out = {}
+        k = 0
+        while True:
+            name = C.create_string_buffer(128)
+            n, ms = C.c_int64(), C.c_double()
+            if self.lib.gc_profile_read(self._h, k, name, 128, C.byref(n), C.byref(ms)) != 0:
+                break
+            out[name.value.decode()] = (n.value, ms.value)
+            k += 1
+        return out
 
     def launch_count(self):
         v = C.c_int64()

@@ -19,6 +19,7 @@
 #include "../../include/gc_b200.h"
 #include "gc_query.cuh"
 #include "gc_tile.cuh"
+#include "gc_peak.cuh"
 
 using namespace gc;
 
@@ -75,6 +76,16 @@ struct gc_ctx {
     // graph cache for the fixed-dt step sequence
     cudaGraphExec_t graph_exec = nullptr;
     int graph_steps = 0;
+
+    // per-kernel event timing (gc_profile_*)
+    struct ProfKernel {
+        std::string name;
+        std::vector<cudaEvent_t> ev;   // begin/end pairs
+    };
+    bool profiling = false;
+    std::vector<ProfKernel> prof;
+    size_t prof_events = 0;
+    int prof_open = -1;
 };
 
 namespace {
@@ -256,6 +267,9 @@ int gc_destroy(gc_ctx *ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
+    for (auto &k : ctx->prof) {
+        for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
+    }
     for (void *p : ctx->allocs) cudaFree(p);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -595,7 +609,49 @@ int gc_set_skin(gc_ctx *ctx, double skin_fraction)
 // ---------------------------------------------------------------------------
 namespace {
 
-#define LAUNCH(ctx, kernel, grid, block, ...)                                                     do {                                                                                              kernel<<<grid, block, 0, (ctx)->stream>>>(__VA_ARGS__);                                       (ctx)->launches++;                                                                        } while (0)
+constexpr size_t PROF_MAX_EVENTS = 40000;
+
+void prof_begin(gc_ctx *ctx, const char *name)
+{
+    ctx->prof_open = -1;
+    if (!ctx->profiling || ctx->prof_events + 2 > PROF_MAX_EVENTS) return;
+    int k = 0;
+    for (; k < (int) ctx->prof.size(); k++) {
+        if (ctx->prof[k].name == name) break;
+    }
+    if (k == (int) ctx->prof.size()) ctx->prof.push_back({name, {}});
+    cudaEvent_t a = nullptr, b = nullptr;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+    ctx->prof[k].ev.push_back(a);
+    ctx->prof[k].ev.push_back(b);
+    ctx->prof_events += 2;
+    ctx->prof_open = k;
+    cudaEventRecord(a, ctx->stream);
+}
+
+void prof_end(gc_ctx *ctx)
+{
+    if (ctx->prof_open < 0) return;
+    cudaEventRecord(ctx->prof[ctx->prof_open].ev.back(), ctx->stream);
+    ctx->prof_open = -1;
+}
+
+void prof_clear(gc_ctx *ctx)
+{
+    for (auto &k : ctx->prof) {
+        for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
+    }
+    ctx->prof.clear();
+    ctx->prof_events = 0;
+}
+
+#define LAUNCH(ctx, kernel, grid, block, ...)                                                 \
+    do {                                                                                      \
+        prof_begin(ctx, #kernel);                                                             \
+        kernel<<<grid, block, 0, (ctx)->stream>>>(__VA_ARGS__);                               \
+        prof_end(ctx);                                                                        \
+        (ctx)->launches++;                                                                    \
+    } while (0)
 
 // Per-bead adjacency in CSR form + parameter upload.
 int finalize(gc_ctx *ctx)
@@ -951,7 +1007,7 @@ int gc_set_contact_map(gc_ctx *ctx, double distance, int64_t interval, int32_t s
     GC_CHECK_CTX(ctx);
     if (!(distance >= 0) || interval < 0) return fail(ctx, GC_ERR_INVALID, "bad args");
     ContactParams &C = ctx->hp.contact;
-    size_t cap = table_capacity ? table_capacity : std::max<size_t>(64 * (size_t) ctx->n, 1 << 16);
+    size_t cap = table_capacity ? table_capacity : std::max<size_t>(256 * (size_t) ctx->n, 1 << 16);
     size_t pow2 = 1;
     while (pow2 < cap) pow2 <<= 1;
     if (!C.keys || C.capacity != pow2) {
@@ -1001,7 +1057,10 @@ int gc_contacts_clear(gc_ctx *ctx)
                                  ctx->stream));
     GC_CUDA(ctx, cudaMemsetAsync(C.used, 0, ctx->n_rep * sizeof(unsigned int), ctx->stream));
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return GC_OK;
+    // a "table full" condition ends with the clear
+    return modify_states(ctx, -1, [&](RepState &st, int) {
+        if (st.error == 2) st.error = 0;
+    });
 }
 
 int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity, size_t *count)
@@ -1155,6 +1214,43 @@ int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16])
     out[10] = st.need_rebuild;
     out[11] = st.parity;
     out[12] = st.sc.dt_cur;
+    return GC_OK;
+}
+
+int gc_measure_fp32_peak(int32_t device, double *tflops)
+{
+    if (!tflops) return GC_ERR_INVALID;
+    *tflops = 0.0;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return GC_ERR_CUDA;
+    return measure_fp32_peak(device, tflops) == cudaSuccess ? GC_OK : GC_ERR_CUDA;
+}
+
+int gc_profile_enable(gc_ctx *ctx, int32_t enabled)
+{
+    GC_CHECK_CTX(ctx);
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (enabled) prof_clear(ctx);
+    ctx->profiling = enabled != 0;
+    return GC_OK;
+}
+
+int gc_profile_read(gc_ctx *ctx, int32_t index, char *name, size_t name_capacity,
+                    int64_t *launches, double *total_ms)
+{
+    GC_CHECK_CTX(ctx);
+    if (index < 0 || index >= (int) ctx->prof.size()) return GC_ERR_INVALID;
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const auto &k = ctx->prof[index];
+    double total = 0.0;
+    for (size_t e = 0; e + 1 < k.ev.size(); e += 2) {
+        float ms = 0.0f;
+        GC_CUDA(ctx, cudaEventElapsedTime(&ms, k.ev[e], k.ev[e + 1]));
+        total += ms;
+    }
+    if (name && name_capacity) snprintf(name, name_capacity, "%s", k.name.c_str());
+    if (launches) *launches = (int64_t) (k.ev.size() / 2);
+    if (total_ms) *total_ms = total;
     return GC_OK;
 }
 

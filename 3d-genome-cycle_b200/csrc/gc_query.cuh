@@ -7,6 +7,7 @@
 namespace gc {
 
 #define GC_EMPTY_KEY 0xffffffffffffffffull
+#define GC_MAX_PROBES 512
 
 __device__ __forceinline__ unsigned long long hash64(unsigned long long k)
 {
@@ -27,7 +28,10 @@ __device__ __forceinline__ void contact_insert(const ContactParams &C, int r, Re
     unsigned long long *keys = C.keys + (size_t) r * C.capacity;
     unsigned int *vals = C.vals + (size_t) r * C.capacity;
     unsigned long long h = hash64(key) & mask;
-    for (unsigned long long probe = 0; probe < C.capacity; probe++) {
+    // Bounded linear probing: a table that is (nearly) full fails fast with
+    // GC_ERR_CAPACITY instead of degenerating into capacity-long scans.
+    if (st.error == 2) return;
+    for (int probe = 0; probe < GC_MAX_PROBES; probe++) {
         unsigned long long cur = keys[h];
         if (cur == GC_EMPTY_KEY) {
             cur = atomicCAS(&keys[h], GC_EMPTY_KEY, key);

@@ -81,6 +81,24 @@ def setup_interphase(sys, design, cfg, wall_ode=True, schedule=True, contacts=Tr
     return terms
 
 
+def begin_relaxation(sys, cfg):
+    """run_relaxation (simulation_driver_relaxation.cpp:8-56): scales and wall stay
+    at their initial values and the callback never touches the contact map."""
+    sys.set_schedule(cfg.core_scale_init, cfg.core_scale_tau, cfg.bond_scale_init,
+                     cfg.bond_scale_tau, enabled=False)
+    sys.set_contact_map(cfg.contactmap_distance, 0, scale_by_core=True)
+
+
+def begin_interphase(sys, cfg):
+    """run_simulation up to and including callback(0)
+    (simulation_driver_interphase.cpp:8-55): schedule and contact cadence on."""
+    sys.set_schedule(cfg.core_scale_init, cfg.core_scale_tau, cfg.bond_scale_init,
+                     cfg.bond_scale_tau, enabled=True)
+    sys.set_contact_map(cfg.contactmap_distance, cfg.contactmap_update_interval,
+                        scale_by_core=True)
+    interphase_callback0(sys, cfg)
+
+
 def interphase_callback0(sys, cfg):
     """callback(0) of run_simulation (simulation_driver_interphase.cpp:55):
     update_core_scale at t = 0 and one wall-ODE step with zero reaction

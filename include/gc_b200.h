@@ -254,6 +254,19 @@ int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
    need_rebuild, parity, dt_cur, 0, 0, 0}. */
 int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16]);
 
+/* ---- measurement (bench.py; no reference counterpart) ------------------- */
+
+/* Per-kernel CUDA-event timing on the context's stream.  While enabled every
+   launch is bracketed by an event pair (slows the step slightly, so it is used
+   in a separate short pass, never inside a timed region).  Enabling resets the
+   record.  gc_profile_read(index) returns GC_ERR_INVALID past the last kernel. */
+int gc_profile_enable(gc_ctx *ctx, int32_t enabled);
+int gc_profile_read(gc_ctx *ctx, int32_t index, char *name, size_t name_capacity,
+                    int64_t *launches, double *total_ms);
+/* Measured non-tensor FP32 peak of `device` (dependent-free FFMA chains on every
+   SM, best of 5), the denominator of the FP32 roofline fraction. */
+int gc_measure_fp32_peak(int32_t device, double *tflops);
+
 /* Number of kernels launched by this context since creation (bench claim). */
 int gc_launch_count(gc_ctx *ctx, int64_t *out);
 /* Block until all queued device work of the context has finished. */
