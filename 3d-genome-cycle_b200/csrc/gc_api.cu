@@ -19,6 +19,7 @@
 #include "../../include/gc_b200.h"
 #include "gc_query.cuh"
 #include "gc_tile.cuh"
+#include "gc_cells.cuh"
 #include "gc_peak.cuh"
 
 using namespace gc;
@@ -208,7 +209,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-        int per_sm = 8;
+        int per_sm = 5;
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = std::max(4, (sms * per_sm + n_replicas - 1) / n_replicas);
         if (const char *env = getenv("GC_KERNEL")) ctx->use_tile = strcmp(env, "walk") != 0;
@@ -233,6 +234,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     if (!rc) rc = dev_alloc(ctx, &P.sab, RN);
     if (!rc) rc = dev_alloc(ctx, &P.members, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_of, RN);
+    if (!rc) rc = dev_alloc(ctx, &P.cell_list, RN);
     if (!rc) rc = dev_alloc(ctx, &P.force, RN);
     if (!rc) rc = dev_alloc(ctx, &P.pforce, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_count, (size_t) n_replicas * P.ncell_max);
@@ -789,7 +791,7 @@ void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
 {
     if (ctx->use_tile) {
         dim3 g(ctx->tile_grid_x, ctx->n_rep);
-        LAUNCH(ctx, k_pair_tile, g, TB, ctx->dp, mask, use_enabled);
+        LAUNCH(ctx, k_pair_cells, g, CW * 32, ctx->dp, mask, use_enabled);
         dim3 gf = bead_grid(ctx, BS);
         if (mode == STEP_FUSED) LAUNCH(ctx, k_finish<STEP_FUSED>, gf, BS, ctx->dp, mask, use_enabled);
         else LAUNCH(ctx, k_finish<STEP_FORCE>, gf, BS, ctx->dp, mask, use_enabled);

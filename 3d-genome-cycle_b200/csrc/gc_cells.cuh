@@ -1,0 +1,221 @@
+// gc_cells.cuh -- nonbonded soft-core forces, warp-per-cell (the production
+// pair kernel).
+//
+// Replaces the pair loop of md::neighbor_pairwise_forcefield
+// (MD/forcefield/neighbor_pairwise_forcefield.hpp:68-84) together with the
+// Verlet list it walks (MD/forcefield/detail/neighbor_list.hpp:162-230): no pair
+// list exists here.  Each WARP pops non-empty home cells from a per-replica work
+// queue (Params::cell_list, filled by k_gather) and, privately, with no block
+// barrier anywhere:
+//   1. lanes 0..8 fetch the slot ranges of the 9 contiguous x-rows of the 27
+//      neighbouring cells (the grid carries a one-cell halo, so there are no
+//      bounds checks); a warp scan flattens them into one candidate list;
+//   2. the warp stages that list into ITS OWN shared-memory tile, coalesced per
+//      row, as (x, y, z, A') + B' with the A/B mixing factors pre-scaled;
+//   3. lanes split into H home beads x S candidate slices (H * S <= 32, chosen per
+//      cell) and evaluate EVERY staged candidate branch-free: the clamped soft
+//      cores vanish identically beyond their diameter, so there is no distance
+//      test, no ballot and no compaction (25 FP32 instructions per pair);
+//   4. S - 1 shuffles per component fold the slices and lanes < H store the force
+//      of their home bead (sorted-slot order, consumed by k_finish).
+// Every bead gathers its own force (full neighbourhood, no atomics), so the
+// result is bit-reproducible and independent of the queue order.
+#pragma once
+
+#include "gc_step.cuh"
+
+namespace gc {
+
+constexpr int CW = 4;                    // warps per block
+constexpr int CCAP = 480;                // candidates per tile chunk
+constexpr int CHMAX = 16;                // home beads per pass
+constexpr int CGROUP = 2 * CHMAX;        // home beads per staged tile (two passes)
+
+// One soft-core pair, branchless (see header).  sA = 0.5 cA (a_i + a_j) and
+// sB = 0.5 cB (b_i + b_j) arrive pre-scaled:
+//   A: 6 eps_A kA2 (1 - u)^2,  B: 24 eps_B kB2 (1 - u^4)^2 u^3   (gc_math.cuh)
+__device__ __forceinline__ void pair_accumulate(float xi, float yi, float zi, float Ai, float Bi,
+                                                float4 q, float Bj, float kA2, float kB2,
+                                                float &fx, float &fy, float &fz)
+{
+    const float ex = xi - q.x, ey = yi - q.y, ez = zi - q.z;
+    const float r2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+    const float gA = fmaxf(fmaf(-r2, kA2, 1.0f), 0.0f);
+    const float uB = r2 * kB2;
+    const float uB2 = uB * uB;
+    const float gB = fmaxf(fmaf(-uB2, uB2, 1.0f), 0.0f);
+    const float tA = gA * gA;
+    const float tB = (gB * gB) * (uB2 * uB);
+    const float fac = fmaf(Bi + Bj, tB, (Ai + q.w) * tA);
+    fx = fmaf(fac, ex, fx);
+    fy = fmaf(fac, ey, fy);
+    fz = fmaf(fac, ez, fz);
+}
+
+struct CellWarpSmem {
+    float4 tile[CCAP];                   // x, y, z, A'
+    float tileB[CCAP];                   // B'
+    int row_off[33];                     // first flattened index of each row (+ sentinel)
+    int row_shift[32];                   // slot = flattened index + row_shift[row]
+};
+
+// Home-bead pass over the staged tile [0, nt): lanes = H beads x S slices,
+// slice s takes candidates s, s + S, s + 2 S, ...
+__device__ __forceinline__ void cell_pass(const CellWarpSmem &sm, int nt, int S, int s,
+                                          float4 me, float Ai, float Bi, float kA2, float kB2,
+                                          float &fx, float &fy, float &fz)
+{
+    const int full = nt / S;             // iterations in which every slice has a candidate
+    const float4 *tq = sm.tile + s;
+    const float *tb = sm.tileB + s;
+#pragma unroll 4
+    for (int it = 0; it < full; it++) {
+        pair_accumulate(me.x, me.y, me.z, Ai, Bi, tq[it * S], tb[it * S], kA2, kB2, fx, fy, fz);
+    }
+    if (s < nt - full * S) {             // ragged tail: the first nt % S slices
+        pair_accumulate(me.x, me.y, me.z, Ai, Bi, tq[full * S], tb[full * S], kA2, kB2, fx, fy, fz);
+    }
+}
+
+// Sum over the S slices of each home bead, in fixed order; valid in lanes < H.
+__device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, float &fy, float &fz)
+{
+    for (int k = 1; k < S; k++) {
+        const int src = (lane + k * H) & 31;
+        const float gx = __shfl_sync(0xffffffffu, fx, src);
+        const float gy = __shfl_sync(0xffffffffu, fy, src);
+        const float gz = __shfl_sync(0xffffffffu, fz, src);
+        if (lane < H) { fx += gx; fy += gy; fz += gz; }
+    }
+}
+
+__global__ void __launch_bounds__(CW * 32) k_pair_cells(Params *Pp, unsigned mask_arg,
+                                                        int use_enabled)
+{
+    __shared__ CellWarpSmem s_warp[CW];
+
+    Params &P = *Pp;
+    const int r = blockIdx.y;
+    RepState &st = P.st[r];
+    const StepConst &sc = st.sc;
+    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
+    const size_t ro = (size_t) r * P.n;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    const float4 *__restrict__ sp = P.spos[st.parity] + ro;
+    const float2 *__restrict__ sab = P.sab + ro;
+    float4 *__restrict__ pforce = P.pforce + ro;
+    const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
+
+    if (!pair_on) {                                            // block-uniform
+        for (int t = blockIdx.x * (CW * 32) + threadIdx.x; t < P.n; t += gridDim.x * (CW * 32)) {
+            pforce[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+
+    const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    const int4 *__restrict__ cells = P.cell_list + ro;
+    const int nused = st.n_used_cells;
+    const int dx = st.dims[0], dxy = st.dims[0] * st.dims[1];
+    const int M = P.cells_per_cut;
+    const int side = 2 * M + 1, nrows = side * side;
+    const bool plain = P.pair.mode == PAIR_PLAIN;
+    const float kA2 = sc.kA2, kB2 = sc.kB2;
+    const float hA = 0.5f * sc.cA, hB = plain ? 0.0f : 0.5f * sc.cB;
+    CellWarpSmem &sm = s_warp[warp];
+    // row `lane` of the (2M+1)^2 neighbour rows, relative to the home cell: the
+    // grid has an M-cell halo (plan_grid), so every row exists
+    const int row_rel = lane < nrows ? (lane % side - M) * dx + (lane / side - M) * dxy - M : 0;
+
+    for (;;) {
+        int kk = 0;
+        if (lane == 0) kk = atomicAdd(&st.cell_cursor, 1);
+        kk = __shfl_sync(0xffffffffu, kk, 0);
+        if (kk >= nused) break;
+        const int4 cell = __ldg(&cells[kk]);
+        const int c = cell.x, h0 = cell.y, nhome = cell.z;
+
+        // ---- 1. candidate rows -> flattened list -------------------------------
+        int lo = 0, len = 0;
+        if (lane < nrows) {
+            lo = __ldg(&start[c + row_rel]);
+            len = __ldg(&start[c + row_rel + side]) - lo;
+        }
+        int incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();                                          // previous cell fully consumed
+        sm.row_off[lane] = incl - len;                         // lanes >= nrows hold `total`
+        sm.row_shift[lane] = lo - (incl - len);
+        if (lane == 0) sm.row_off[32] = total;
+        __syncwarp();
+
+        for (int g0 = 0; g0 < nhome; g0 += CGROUP) {           // home beads, <= 32 per tile
+            const int ng = min(CGROUP, nhome - g0);
+            // pass a: beads [g0, g0 + Ha), pass b: beads [g0 + Ha, g0 + ng)
+            const int Ha = min(CHMAX, ng), Hb = ng - Ha;
+            const int Sa = 32 / Ha, Sb = Hb > 0 ? 32 / Hb : 1;
+            const int sa = (lane * (65536 / Ha + 1)) >> 16, ha = lane - sa * Ha;
+            const int sb = Hb > 0 ? (lane * (65536 / Hb + 1)) >> 16 : 0;
+            const int hb = Hb > 0 ? lane - sb * Hb : 0;
+            const float4 ma = __ldg(&sp[h0 + g0 + ha]);
+            const int ib = Hb > 0 ? g0 + Ha + hb : g0;         // pass b idles on bead g0
+            const float4 mb = __ldg(&sp[h0 + ib]);
+            float Aa = hA, Ba = 0.0f, Ab = hA, Bb = 0.0f;
+            if (!plain) {
+                const float2 aba = __ldg(&sab[h0 + g0 + ha]);
+                const float2 abb = __ldg(&sab[h0 + ib]);
+                Aa = hA * aba.x; Ba = hB * aba.y;
+                Ab = hA * abb.x; Bb = hB * abb.y;
+            }
+            float fax = 0.f, fay = 0.f, faz = 0.f, fbx = 0.f, fby = 0.f, fbz = 0.f;
+
+            for (int c0 = 0; c0 < total; c0 += CCAP) {         // tile chunks (usually one)
+                const int nt = min(CCAP, total - c0);
+                if (c0 > 0 || g0 > 0) __syncwarp();            // previous tile fully consumed
+                // ---- 2. stage the chunk: flattened, coalesced within each row ----
+                {
+                    int row = 0, end = sm.row_off[1], shift = sm.row_shift[0];
+                    for (int k = c0 + lane; k < c0 + nt; k += 32) {
+                        if (k >= end) {
+                            do {
+                                row++;
+                                end = sm.row_off[row + 1];
+                            } while (k >= end);
+                            shift = sm.row_shift[row];
+                        }
+                        float4 q = __ldg(&sp[k + shift]);
+                        float qB = 0.0f;
+                        if (plain) {
+                            q.w = hA;
+                        } else {
+                            const float2 ab = __ldg(&sab[k + shift]);
+                            q.w = hA * ab.x;
+                            qB = hB * ab.y;
+                        }
+                        sm.tile[k - c0] = q;
+                        sm.tileB[k - c0] = qB;
+                    }
+                }
+                __syncwarp();
+                // ---- 3. H home beads x S slices, branch-free -----------------------
+                cell_pass(sm, nt, Sa, sa, ma, Aa, Ba, kA2, kB2, fax, fay, faz);
+                if (Hb > 0) cell_pass(sm, nt, Sb, sb, mb, Ab, Bb, kA2, kB2, fbx, fby, fbz);
+            }
+            // ---- 4. fold the slices, store -----------------------------------------
+            cell_fold(Ha, Sa, lane, fax, fay, faz);
+            if (lane < Ha) pforce[h0 + g0 + lane] = make_float4(fax, fay, faz, 0.0f);
+            if (Hb > 0) {
+                cell_fold(Hb, Sb, lane, fbx, fby, fbz);
+                if (lane < Hb) pforce[h0 + g0 + Ha + lane] = make_float4(fbx, fby, fbz, 0.0f);
+            }
+        }
+    }
+}
+
+} // namespace gc

@@ -58,24 +58,27 @@ __device__ __forceinline__ PairCoef make_pair_coef(double eps_a, double sigma_a,
     return c;
 }
 
-__device__ __forceinline__ int cell_coord(float x, float origin, float inv, int dim)
+// The grid carries a halo of `halo` (= cells_per_cut) always-empty cells on every
+// side, so neighbourhood walks need no bounds checks.
+__device__ __forceinline__ int cell_coord(float x, float origin, float inv, int dim, int halo)
 {
     int c = (int) floorf((x - origin) * inv);
-    return min(max(c, 0), dim - 1);
+    return min(max(c, halo), dim - 1 - halo);
 }
 
-__device__ __forceinline__ int cell_index(const RepState &st, float4 p)
+__device__ __forceinline__ int cell_index(const RepState &st, float4 p, int halo)
 {
-    int cx = cell_coord(p.x, st.origin[0], st.inv_cell, st.dims[0]);
-    int cy = cell_coord(p.y, st.origin[1], st.inv_cell, st.dims[1]);
-    int cz = cell_coord(p.z, st.origin[2], st.inv_cell, st.dims[2]);
+    int cx = cell_coord(p.x, st.origin[0], st.inv_cell, st.dims[0], halo);
+    int cy = cell_coord(p.y, st.origin[1], st.inv_cell, st.dims[1], halo);
+    int cz = cell_coord(p.z, st.origin[2], st.inv_cell, st.dims[2], halo);
     return cx + st.dims[0] * (cy + st.dims[1] * cz);
 }
 
 // Chooses origin / cell size / dims from the bounding box for list radius
-// `rlist`.  Cells outside the box are folded into the boundary cells by
-// clamping, which never separates two beads further than their true cell
-// distance, so no pair within rlist can be missed.
+// `rlist`, plus a halo of cells_per_cut empty cells on every side.  Beads
+// outside the box are folded into the outermost interior cells by clamping,
+// which never separates two beads further than their true cell distance, so no
+// pair within rlist can be missed.
 __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
 {
     float lo[3], hi[3];
@@ -95,7 +98,7 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
         double tot = 1.0;
         for (int k = 0; k < 3; k++) {
             double e = (double) hi[k] - (double) lo[k];
-            double d = floor(e / cs) + 1.0;
+            double d = floor(e / cs) + 1.0 + 2.0 * P.cells_per_cut;
             if (d > 1.0e6) d = 1.0e6;
             dims[k] = (int) d;
             tot *= d;
@@ -105,7 +108,7 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
     }
     for (int k = 0; k < 3; k++) {
         st.dims[k] = dims[k];
-        st.origin[k] = lo[k];
+        st.origin[k] = (float) ((double) lo[k] - cs * P.cells_per_cut);
     }
     st.ncell = dims[0] * dims[1] * dims[2];
     st.cell_size = (float) cs;
@@ -135,6 +138,7 @@ __global__ void k_reset_reductions(Params *Pp)
     st.maxdisp2_bits = 0u;
     st.dtmin_bits = 0x7f800000u;
     st.ticket = 0u;
+    st.cell_cursor = 0;
 }
 
 __global__ void k_bbox(Params *Pp)
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(256) k_count(Params *Pp)
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
     float4 p = P.pos[st.parity][(size_t) r * P.n + i];
-    int c = cell_index(st, p);
+    int c = cell_index(st, p, P.cells_per_cut);
     P.cell_of[(size_t) r * P.n + i] = c;
     atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
 }
@@ -194,8 +198,9 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan(Params *Pp)
 {
     Params &P = *Pp;
     int r = blockIdx.x;
-    const RepState &st = P.st[r];
+    RepState &st = P.st[r];
     if (!st.need_rebuild) return;
+    if (threadIdx.x == 0) st.n_used_cells = 0;          // k_gather refills the list
     int *count = P.cell_count + (size_t) r * P.ncell_max;
     int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
     int ncell = st.ncell;
@@ -254,7 +259,7 @@ __global__ void __launch_bounds__(256) k_gather(Params *Pp)
 {
     Params &P = *Pp;
     int r = blockIdx.y;
-    const RepState &st = P.st[r];
+    RepState &st = P.st[r];
     if (!st.need_rebuild) return;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P.n) return;
@@ -266,7 +271,12 @@ __global__ void __launch_bounds__(256) k_gather(Params *Pp)
     int base = start[c], end = start[c + 1];
     int rank = 0;
     for (int k = base; k < end; k++) rank += members[k] < idx;
-    if (rank == 0) P.cell_count[(size_t) r * P.ncell_max + c] = 0;   // cursor back to 0
+    if (rank == 0) {
+        P.cell_count[(size_t) r * P.ncell_max + c] = 0;   // cursor back to 0
+        // work queue of the pair kernel; its order is arbitrary but no result depends on it
+        int e = atomicAdd(&st.n_used_cells, 1);
+        P.cell_list[ro + e] = make_int4(c, base, end - base, 0);
+    }
     int dst = base + rank;
     float4 p = P.pos[st.parity][ro + idx];
     p.w = __int_as_float(idx);

@@ -414,6 +414,7 @@ __device__ inline void finalize_step(const Params &P, RepState &st, double dt_us
     }
     st.dtmin_bits = 0x7f800000u;
     st.ticket = 0u;
+    st.cell_cursor = 0;
     refresh_consts(P, st);
 }
 
@@ -626,6 +627,7 @@ __global__ void __launch_bounds__(SBS) k_step(Params *Pp, unsigned mask_arg, int
             st.sc.dt_cur = dtc;
             st.dtmin_bits = 0x7f800000u;
             st.ticket = 0u;
+            st.cell_cursor = 0;
         }
     }
 }
@@ -666,6 +668,7 @@ __global__ void k_plan(Params *Pp, double radius_override)
     st.need_rebuild = 1;
     st.maxdisp2_bits = 0u;
     st.rebuilds += 1;
+    st.cell_cursor = 0;
     // the next step accumulates its own bounding box from scratch
     for (int k = 0; k < 3; k++) {
         st.bbox_min[k] = 0x7fffffff;

@@ -7,6 +7,7 @@
 //   sidx / scell / slot_of [R][N] int32  sorted<->original maps, cell of each slot
 //   sab    [R][N] float2   (a, b) factors gathered into sorted order
 //   cell_count / cell_start [R][ncell_max(+1)] int32
+//   cell_list [R][N] int4   non-empty cells (the pair kernel's work queue)
 //   force  [R][N] float4   only for the adaptive stepper / gc_compute_force
 //   st     [R]    RepState per-replica scalars (schedule, wall, reductions)
 // Bead attributes and bonded topology are shared by all replicas.
@@ -130,6 +131,8 @@ struct RepState {
     unsigned int dtmin_bits;       // adaptive dt candidate (float bits)
     int bbox_min[3], bbox_max[3];  // order-preserving int encoding of floats
     unsigned int ticket;
+    int n_used_cells;              // entries of Params::cell_list (non-empty cells)
+    int cell_cursor;               // work-queue head of the pair kernel, reset every step
     // --- cell grid ---
     int need_rebuild;
     int parity;                    // which ping-pong buffer holds current positions
@@ -172,6 +175,7 @@ struct Params {
     int *sidx, *scell, *slot_of;
     float2 *sab;
     int *cell_count, *cell_start, *members, *cell_of;
+    int4 *cell_list;               // [R][N] non-empty cells {cell, first slot, beads, 0}
     float4 *force;                 // total force, ORIGINAL order (adaptive stepper, gc_compute_force)
     float4 *pforce;                // nonbonded force, SORTED order (k_pair_tile -> k_finish)
     RepState *st;
