@@ -12,7 +12,7 @@ from pathlib import Path
 import numpy as np
 
 PKG_DIR = Path(__file__).resolve().parent
-LIB_PATH = PKG_DIR / "libgc_b200.so"
+LIB_PATH = Path(os.environ.get("GC_B200_LIB", PKG_DIR / "libgc_b200.so"))
 
 GC_BOND_SEMISPRING, GC_BOND_HARMONIC, GC_BOND_SPRING = 0, 1, 2
 GC_SOURCE_SEMISPRING, GC_SOURCE_FORCE_FLUX = 0, 1

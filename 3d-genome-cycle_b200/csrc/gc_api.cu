@@ -37,8 +37,7 @@ struct gc_ctx {
     int n = 0, n_rep = 1;
     std::string error;
 
-    Params hp{};            // host mirror
-    Params *dp = nullptr;   // device copy read by every kernel
+    Params hp{};            // passed BY VALUE to every kernel (__grid_constant__)
     bool params_dirty = true;
     bool topo_dirty = true;
     bool attrs_set = false;
@@ -70,13 +69,8 @@ struct gc_ctx {
     int parity = 0;             // host mirror of RepState::parity (replicas move in lockstep)
     long long launches = 0;
     double skin = 0.0;
-    int use_graph = 0;
-    int use_tile = 1;           // cell-tile step kernel (0: warp-per-bead walk)
-    int tile_grid_x = 1;        // blocks per replica of the cell-tile kernel
+    int tile_grid_x = 1;        // blocks per replica of the pair kernel
 
-    // graph cache for the fixed-dt step sequence
-    cudaGraphExec_t graph_exec = nullptr;
-    int graph_steps = 0;
 
     // per-kernel event timing (gc_profile_*)
     struct ProfKernel {
@@ -202,6 +196,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     {
         long long want = std::max<long long>(8LL * n_beads, 32768);
         want = std::min<long long>(want, 1LL << 23);
+        want = (want + 3) & ~3LL;                // k_scan reads the counts as int4
         P.ncell_max = (int) want;
     }
     P.cells_per_cut = 1;
@@ -212,7 +207,6 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         int per_sm = 5;
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = std::max(4, (sms * per_sm + n_replicas - 1) / n_replicas);
-        if (const char *env = getenv("GC_KERNEL")) ctx->use_tile = strcmp(env, "walk") != 0;
     }
     P.skin = 0.0f;
     P.kT = 1.0f;
@@ -228,19 +222,18 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         if (!rc) rc = dev_alloc(ctx, &P.spos[k], RN);
     }
     if (!rc) rc = dev_alloc(ctx, &P.sref, RN);
-    if (!rc) rc = dev_alloc(ctx, &P.sidx, RN);
     if (!rc) rc = dev_alloc(ctx, &P.scell, RN);
-    if (!rc) rc = dev_alloc(ctx, &P.slot_of, RN);
     if (!rc) rc = dev_alloc(ctx, &P.sab, RN);
     if (!rc) rc = dev_alloc(ctx, &P.members, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_of, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_list, RN);
+    P.scan_blocks = (P.ncell_max + SCAN_TILE - 1) / SCAN_TILE;
+    if (!rc) rc = dev_alloc(ctx, &P.scan_status, (size_t) n_replicas * P.scan_blocks);
     if (!rc) rc = dev_alloc(ctx, &P.force, RN);
     if (!rc) rc = dev_alloc(ctx, &P.pforce, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_count, (size_t) n_replicas * P.ncell_max);
     if (!rc) rc = dev_alloc(ctx, &P.cell_start, (size_t) n_replicas * (P.ncell_max + 1));
     if (!rc) rc = dev_alloc(ctx, &P.st, (size_t) n_replicas);
-    if (!rc) rc = dev_alloc(ctx, &ctx->dp, 1);
     if (!rc) rc = dev_alloc(ctx, &ctx->d_partials, (size_t) (n_beads + BS - 1) / BS + 1);
     if (!rc) rc = dev_alloc(ctx, &ctx->d_counter, 4);
     if (!rc) rc = dev_alloc(ctx, &ctx->d_mob, (size_t) n_beads);
@@ -268,7 +261,6 @@ int gc_destroy(gc_ctx *ctx)
     if (!ctx) return GC_ERR_INVALID;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
     for (auto &k : ctx->prof) {
         for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
     }
@@ -664,7 +656,17 @@ int finalize(gc_ctx *ctx)
     if (ctx->topo_dirty) {
         std::vector<int> flags((size_t) n, 0);
         std::vector<int> boff((size_t) n + 1, 0), toff((size_t) n + 1, 0), koff((size_t) n + 1, 0);
-        for (auto &b : ctx->bonds) { boff[b.i + 1]++; boff[b.j + 1]++; }
+        // Harmonic bonds with K == 0 exert exactly zero force and energy (the
+        // reference's loop bonds, SURVEY 8a note on a12): keep the term id but do
+        // not iterate them on the device.
+        std::vector<HostBond> live;
+        live.reserve(ctx->bonds.size());
+        for (auto &b : ctx->bonds) {
+            const BondTerm &bt = P.bonds[b.bterm];
+            if (bt.kind == GC_BOND_HARMONIC && bt.K_a == 0.0 && bt.K_b == 0.0) continue;
+            live.push_back(b);
+        }
+        for (auto &b : live) { boff[b.i + 1]++; boff[b.j + 1]++; }
         for (auto &t : ctx->triples) { toff[t.i + 1]++; toff[t.j + 1]++; toff[t.k + 1]++; }
         for (auto &k : ctx->tethers) koff[k.bead + 1]++;
         for (int i = 0; i < n; i++) {
@@ -677,7 +679,7 @@ int finalize(gc_ctx *ctx)
         std::vector<TetherEntry> kent((size_t) koff[n]);
         {
             std::vector<int> cur(boff.begin(), boff.end() - 1);
-            for (auto &b : ctx->bonds) {
+            for (auto &b : live) {
                 bent[cur[b.i]++] = {b.j, b.bterm};
                 bent[cur[b.j]++] = {b.i, b.bterm};
             }
@@ -722,16 +724,7 @@ int finalize(gc_ctx *ctx)
         ctx->topo_dirty = false;
         ctx->params_dirty = true;
     }
-    if (ctx->params_dirty) {
-        GC_CUDA(ctx, cudaMemcpyAsync(ctx->dp, &P, sizeof(Params), cudaMemcpyHostToDevice,
-                                     ctx->stream));
-        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        ctx->params_dirty = false;
-        if (ctx->graph_exec) {   // parameters are read through dp, but be conservative
-            cudaGraphExecDestroy(ctx->graph_exec);
-            ctx->graph_exec = nullptr;
-        }
-    }
+    ctx->params_dirty = false;
     return GC_OK;
 }
 
@@ -739,20 +732,20 @@ int finalize(gc_ctx *ctx)
 int plan_and_rebuild(gc_ctx *ctx, double radius_override)
 {
     const int R = ctx->n_rep;
-    LAUNCH(ctx, k_reset_reductions, (R + 63) / 64, 64, ctx->dp);
+    LAUNCH(ctx, k_reset_reductions, (R + 63) / 64, 64, ctx->hp);
     int bx = std::min((ctx->n + 255) / 256, 1024);
-    LAUNCH(ctx, k_bbox, dim3(std::max(bx, 1), R), 256, ctx->dp);
-    LAUNCH(ctx, k_plan, (R + 63) / 64, 64, ctx->dp, radius_override);
+    LAUNCH(ctx, k_bbox, dim3(std::max(bx, 1), R), 256, ctx->hp);
+    LAUNCH(ctx, k_plan, (R + 63) / 64, 64, ctx->hp, radius_override);
     return GC_OK;
 }
 
 void launch_rebuild(gc_ctx *ctx)
 {
     dim3 g = bead_grid(ctx, 256);
-    LAUNCH(ctx, k_count, g, 256, ctx->dp);
-    LAUNCH(ctx, k_scan, ctx->n_rep, SCAN_BS, ctx->dp);
-    LAUNCH(ctx, k_fill, g, 256, ctx->dp);
-    LAUNCH(ctx, k_gather, g, 256, ctx->dp);
+    LAUNCH(ctx, k_count, g, 256, ctx->hp);
+    LAUNCH(ctx, k_scan, dim3(ctx->hp.scan_blocks, ctx->n_rep), SCAN_BS, ctx->hp);
+    LAUNCH(ctx, k_fill, g, 256, ctx->hp);
+    LAUNCH(ctx, k_gather, g, 256, ctx->hp);
 }
 
 int check_device_errors(gc_ctx *ctx)
@@ -775,9 +768,8 @@ int check_device_errors(gc_ctx *ctx)
     return GC_OK;
 }
 
-__global__ void k_restart(Params *Pp, double dt)
+__global__ void k_restart(const __grid_constant__ Params P, double dt)
 {
-    Params &P = *Pp;
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];
@@ -789,16 +781,16 @@ __global__ void k_restart(Params *Pp, double dt)
 // one force evaluation (+ update when fused) for every replica
 void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
 {
-    if (ctx->use_tile) {
-        dim3 g(ctx->tile_grid_x, ctx->n_rep);
-        LAUNCH(ctx, k_pair_cells, g, CW * 32, ctx->dp, mask, use_enabled);
-        dim3 gf = bead_grid(ctx, BS);
-        if (mode == STEP_FUSED) LAUNCH(ctx, k_finish<STEP_FUSED>, gf, BS, ctx->dp, mask, use_enabled);
-        else LAUNCH(ctx, k_finish<STEP_FORCE>, gf, BS, ctx->dp, mask, use_enabled);
+    dim3 g(ctx->tile_grid_x, ctx->n_rep);
+    LAUNCH(ctx, k_pair_cells, g, CW * 32, ctx->hp, mask, use_enabled);
+    dim3 gf = bead_grid(ctx, BS);
+    const int gr = ctx->n_rep;
+    if (mode == STEP_FUSED) {
+        LAUNCH(ctx, k_finish<STEP_FUSED>, gf, BS, ctx->hp, mask, use_enabled);
+        LAUNCH(ctx, k_finalize_step, gr, 32, ctx->hp, 0);
     } else {
-        dim3 g = bead_grid(ctx, SBEADS);
-        if (mode == STEP_FUSED) LAUNCH(ctx, k_step<STEP_FUSED>, g, SBS, ctx->dp, mask, use_enabled);
-        else LAUNCH(ctx, k_step<STEP_FORCE>, g, SBS, ctx->dp, mask, use_enabled);
+        LAUNCH(ctx, k_finish<STEP_FORCE>, gf, BS, ctx->hp, mask, use_enabled);
+        LAUNCH(ctx, k_finalize_force, gr, 32, ctx->hp);
     }
 }
 
@@ -859,7 +851,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     if (rc) return rc;
 
     if (c->restart) {
-        LAUNCH(ctx, k_restart, (ctx->n_rep + 63) / 64, 64, ctx->dp, c->timestep);
+        LAUNCH(ctx, k_restart, (ctx->n_rep + 63) / 64, 64, ctx->hp, c->timestep);
         ctx->run_step = 0;
     }
     plan_and_rebuild(ctx, 0.0);
@@ -872,12 +864,13 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
         // contact update of the driver callback for the step just finished
         // (SIM/stage_interphase/simulation_driver_interphase.cpp:38-40)
         if (interval > 0 && ctx->run_step > 0 && ctx->run_step % interval == 0 && i > 0) {
-            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
                    (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
         }
         if (adaptive) {
             launch_step(ctx, STEP_FORCE, 0u, 1);
-            LAUNCH(ctx, k_integrate, g, BS, ctx->dp);
+            LAUNCH(ctx, k_integrate, g, BS, ctx->hp);
+            LAUNCH(ctx, k_finalize_step, ctx->n_rep, 32, ctx->hp, 1);
         } else {
             launch_step(ctx, STEP_FUSED, 0u, 1);
         }
@@ -887,7 +880,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     // the callback of the last step of this chunk
     if (interval > 0 && c->steps > 0 && ctx->run_step % interval == 0) {
         launch_rebuild(ctx);
-        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
+        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
                (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
     }
     return check_device_errors(ctx);
@@ -902,7 +895,7 @@ int gc_debug_noise(gc_ctx *ctx, int32_t replica, int64_t step, float *out)
     float *d = nullptr;
     rc = dev_alloc(ctx, &d, (size_t) ctx->n * 3);
     if (rc) return rc;
-    LAUNCH(ctx, k_debug_noise, (ctx->n + 255) / 256, 256, ctx->dp, replica, (long long) step, d);
+    LAUNCH(ctx, k_debug_noise, (ctx->n + 255) / 256, 256, ctx->hp, replica, (long long) step, d);
     GC_CUDA(ctx, cudaMemcpyAsync(out, d, (size_t) ctx->n * 3 * sizeof(float),
                                  cudaMemcpyDeviceToHost, ctx->stream));
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -941,7 +934,7 @@ int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
     int nb = (ctx->n + BS - 1) / BS;
-    LAUNCH(ctx, k_energy, std::max(nb, 1), BS, ctx->dp, replica, term_mask, ctx->d_partials);
+    LAUNCH(ctx, k_energy, std::max(nb, 1), BS, ctx->hp, replica, term_mask, ctx->d_partials);
     std::vector<double> part((size_t) std::max(nb, 1));
     GC_CUDA(ctx, cudaMemcpyAsync(part.data(), ctx->d_partials, part.size() * sizeof(double),
                                  cudaMemcpyDeviceToHost, ctx->stream));
@@ -974,7 +967,7 @@ int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pai
     rc = dev_alloc(ctx, &d_out, capacity);
     if (rc) return rc;
     GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
-    LAUNCH(ctx, k_pairs<PAIRS_LIST>, bead_grid(ctx, SBEADS), SBS, ctx->dp, radius, (int) RADIUS_ARG,
+    LAUNCH(ctx, k_pairs<PAIRS_LIST>, bead_grid(ctx, SBEADS), SBS, ctx->hp, radius, (int) RADIUS_ARG,
            replica, d_out, (unsigned long long) capacity, ctx->d_counter);
     unsigned long long found = 0;
     GC_CUDA(ctx, cudaMemcpyAsync(&found, ctx->d_counter, sizeof found, cudaMemcpyDeviceToHost,
@@ -1043,7 +1036,7 @@ int gc_contacts_update(gc_ctx *ctx)
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->dp, 0.0, (int) RADIUS_CONTACT,
+    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT,
            -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
     return check_device_errors(ctx);
 }
@@ -1101,7 +1094,7 @@ int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capaci
     if (rc) { cleanup(); return rc; }
 
     GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
-    LAUNCH(ctx, k_contact_compact, 148 * 8, 256, ctx->dp, replica, k_in, v_in, ctx->d_counter);
+    LAUNCH(ctx, k_contact_compact, 148 * 8, 256, ctx->hp, replica, k_in, v_in, ctx->d_counter);
 
     // sort by key = (i << 32 | j): the order contact_map::accumulate produces
     // (SIM/stage_interphase/contact_map.cpp:75-82)
@@ -1186,7 +1179,7 @@ int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges, const 
     if (rc) return rc;
     GC_CUDA(ctx, cudaMemcpyAsync(d_ranges, ranges, (size_t) 2 * n_ranges * sizeof(int),
                                  cudaMemcpyHostToDevice, ctx->stream));
-    LAUNCH(ctx, k_rg2, n_ranges, 256, ctx->dp, replica, n_ranges, d_ranges, d_out);
+    LAUNCH(ctx, k_rg2, n_ranges, 256, ctx->hp, replica, n_ranges, d_ranges, d_out);
     GC_CUDA(ctx, cudaMemcpyAsync(out_rg2, d_out, (size_t) n_ranges * sizeof(double),
                                  cudaMemcpyDeviceToHost, ctx->stream));
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

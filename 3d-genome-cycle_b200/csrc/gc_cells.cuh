@@ -89,12 +89,10 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
     }
 }
 
-__global__ void __launch_bounds__(CW * 32) k_pair_cells(Params *Pp, unsigned mask_arg,
+__global__ void __launch_bounds__(CW * 32) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
     __shared__ CellWarpSmem s_warp[CW];
-
-    Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const StepConst &sc = st.sc;

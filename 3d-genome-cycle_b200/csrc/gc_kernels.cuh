@@ -123,9 +123,8 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
 // bounding box + grid planning (run start, explicit force / pair queries)
 // ---------------------------------------------------------------------------
 
-__global__ void k_reset_reductions(Params *Pp)
+__global__ void k_reset_reductions(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];
@@ -137,13 +136,11 @@ __global__ void k_reset_reductions(Params *Pp)
     st.reaction_fx = 0;
     st.maxdisp2_bits = 0u;
     st.dtmin_bits = 0x7f800000u;
-    st.ticket = 0u;
     st.cell_cursor = 0;
 }
 
-__global__ void k_bbox(Params *Pp)
+__global__ void k_bbox(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     int r = blockIdx.y;
     RepState &st = P.st[r];
     const float4 *pos = P.pos[st.parity] + (size_t) r * P.n;
@@ -180,13 +177,15 @@ __global__ void k_bbox(Params *Pp)
 // beads inside a cell end up ordered by original index)
 // ---------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(256) k_count(Params *Pp)
+__global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     int r = blockIdx.y;
     const RepState &st = P.st[r];
     if (!st.need_rebuild) return;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    // reset the scan's look-back words, its ticket and the used-cell list
+    if (i < P.scan_blocks) P.scan_status[(size_t) r * P.scan_blocks + i] = 0ull;
+    if (i == 0) { P.st[r].scan_ticket = 0; P.st[r].n_used_cells = 0; }
     if (i >= P.n) return;
     float4 p = P.pos[st.parity][(size_t) r * P.n + i];
     int c = cell_index(st, p, P.cells_per_cut);
@@ -194,56 +193,110 @@ __global__ void __launch_bounds__(256) k_count(Params *Pp)
     atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
 }
 
-__global__ void __launch_bounds__(SCAN_BS) k_scan(Params *Pp)
+// Exclusive scan of the cell counts: chained multi-block scan with decoupled
+// look-back.  A block takes a ticket (so that every predecessor it may wait for
+// has already been scheduled), scans SCAN_TILE cells, publishes its aggregate,
+// looks back over its predecessors' (aggregate | inclusive prefix) words, then
+// writes the cell starts.  Status words and the ticket are reset by k_count.
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_BS * SCAN_ITEMS;
+constexpr unsigned long long SCAN_AGG = 1ull << 62, SCAN_PREFIX = 2ull << 62;
+constexpr unsigned long long SCAN_VALUE = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(SCAN_BS) k_scan(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
-    int r = blockIdx.x;
+    const int r = blockIdx.y;
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;
-    if (threadIdx.x == 0) st.n_used_cells = 0;          // k_gather refills the list
-    int *count = P.cell_count + (size_t) r * P.ncell_max;
-    int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
-    int ncell = st.ncell;
-
     __shared__ int warp_sums[SCAN_BS / 32];
-    __shared__ int carry;
-    if (threadIdx.x == 0) carry = 0;
+    __shared__ int sh_bid, sh_excl;
+    if (threadIdx.x == 0) sh_bid = atomicAdd(&st.scan_ticket, 1);
     __syncthreads();
+    const int bid = sh_bid;
+    const int ncell = st.ncell;
+    const int base = bid * SCAN_TILE;
+    if (base >= ncell) return;                               // block-uniform
 
-    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    for (int base = 0; base < ncell; base += SCAN_BS) {
-        int c = base + threadIdx.x;
-        int v = c < ncell ? count[c] : 0;
-        if (c < ncell) count[c] = 0;           // ready for k_fill's cursor
-        int x = v;
-        for (int o = 1; o < 32; o <<= 1) {
-            int y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
-        }
-        if (lane == 31) warp_sums[wid] = x;
-        __syncthreads();
-        if (wid == 0) {
-            int w = warp_sums[lane];
-            for (int o = 1; o < 32; o <<= 1) {
-                int y = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += y;
-            }
-            warp_sums[lane] = w;               // inclusive over warps
-        }
-        __syncthreads();
-        int warp_off = wid == 0 ? 0 : warp_sums[wid - 1];
-        int excl = carry + warp_off + x - v;
-        if (c < ncell) start[c] = excl;
-        __syncthreads();
-        if (threadIdx.x == SCAN_BS - 1) carry = excl + v;
-        __syncthreads();
+    int *count = P.cell_count + (size_t) r * P.ncell_max;   // 16-byte aligned: ncell_max % 4 == 0
+    int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    unsigned long long *status = P.scan_status + (size_t) r * P.scan_blocks;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+
+    const int c = base + threadIdx.x * SCAN_ITEMS;
+    int4 v = make_int4(0, 0, 0, 0);
+    if (c + 3 < ncell) {
+        v = *reinterpret_cast<const int4 *>(count + c);
+        *reinterpret_cast<int4 *>(count + c) = make_int4(0, 0, 0, 0);   // k_fill's cursors
+    } else {
+        if (c < ncell) { v.x = count[c]; count[c] = 0; }
+        if (c + 1 < ncell) { v.y = count[c + 1]; count[c + 1] = 0; }
+        if (c + 2 < ncell) { v.z = count[c + 2]; count[c + 2] = 0; }
     }
-    if (threadIdx.x == 0) start[ncell] = carry;
+    const int tsum = v.x + v.y + v.z + v.w;
+    int x = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        int w = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += y;
+        }
+        warp_sums[lane] = w;                                 // inclusive over warps
+        const int aggregate = __shfl_sync(0xffffffffu, w, 31);
+
+        // ---- publish, look back (warp 0) ---------------------------------------
+        int excl = 0;
+        if (bid == 0) {
+            if (lane == 0) atomicExch(&status[0], SCAN_PREFIX | (unsigned long long) aggregate);
+        } else {
+            if (lane == 0) atomicExch(&status[bid], SCAN_AGG | (unsigned long long) aggregate);
+            int pos = bid - 1;
+            for (;;) {
+                const int p = pos - lane;
+                unsigned long long sw = SCAN_PREFIX;         // virtual predecessor of block 0
+                if (p >= 0) sw = *(volatile unsigned long long *) &status[p];
+                const unsigned ready = __ballot_sync(0xffffffffu, (sw >> 62) != 0);
+                const unsigned pref = __ballot_sync(0xffffffffu, (sw >> 62) == 2);
+                // lanes closer than the first inclusive prefix must all be published
+                const int first = pref ? __ffs(pref) - 1 : 32;
+                const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1u);
+                if ((ready & need) != need) continue;        // spin: predecessors are running
+                int val = (lane <= first) ? (int) (sw & SCAN_VALUE) : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                excl += val;
+                if (pref) break;
+                pos -= 32;
+            }
+            if (lane == 0) {
+                atomicExch(&status[bid], SCAN_PREFIX | (unsigned long long) (excl + aggregate));
+            }
+        }
+        if (lane == 0) sh_excl = excl;
+    }
+    __syncthreads();
+    const int warp_off = wid == 0 ? 0 : warp_sums[wid - 1];
+    int e = sh_excl + warp_off + x - tsum;   // exclusive prefix of this thread's first cell
+    if (c < ncell) start[c] = e;
+    e += v.x;
+    if (c + 1 < ncell) start[c + 1] = e;
+    e += v.y;
+    if (c + 2 < ncell) start[c + 2] = e;
+    e += v.z;
+    if (c + 3 < ncell) start[c + 3] = e;
+    e += v.w;
+    if (c <= ncell - 1 && ncell - 1 <= c + 3) start[ncell] = e;   // the thread owning the last cell
 }
 
-__global__ void __launch_bounds__(256) k_fill(Params *Pp)
+__global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     int r = blockIdx.y;
     const RepState &st = P.st[r];
     if (!st.need_rebuild) return;
@@ -255,9 +308,8 @@ __global__ void __launch_bounds__(256) k_fill(Params *Pp)
     P.members[(size_t) r * P.n + s] = i;
 }
 
-__global__ void __launch_bounds__(256) k_gather(Params *Pp)
+__global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     int r = blockIdx.y;
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;
@@ -281,10 +333,8 @@ __global__ void __launch_bounds__(256) k_gather(Params *Pp)
     float4 p = P.pos[st.parity][ro + idx];
     p.w = __int_as_float(idx);
     P.spos[st.parity][ro + dst] = p;
-    P.sref[ro + dst] = p;
-    P.sidx[ro + dst] = idx;
+    if (P.skin > 0.0f) P.sref[ro + dst] = p;
     P.scell[ro + dst] = c;
-    P.slot_of[ro + idx] = dst;
     P.sab[ro + dst] = P.ab[idx];
 }
 

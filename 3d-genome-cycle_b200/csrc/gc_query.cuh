@@ -2,6 +2,7 @@
 // potential energy, observables.  Same cell walk as the force kernel.
 #pragma once
 
+#include "gc_pairwalk.cuh"
 #include "gc_step.cuh"
 
 namespace gc {
@@ -49,6 +50,11 @@ __device__ __forceinline__ void contact_insert(const ContactParams &C, int r, Re
     atomicExch(&st.error, 2);   // table full
 }
 
+constexpr int SBS = 256;                 // threads per block of k_pairs
+constexpr int SWARPS = SBS / 32;
+constexpr int SBEADS = 32;               // beads per block
+constexpr int SPERWARP = SBEADS / SWARPS;
+
 enum PairsMode : int { PAIRS_LIST = 0, PAIRS_CONTACT = 1 };
 enum RadiusSel : int { RADIUS_ARG = 0, RADIUS_CONTACT = 1, RADIUS_CONTACT_PREV = 2 };
 
@@ -59,13 +65,12 @@ enum RadiusSel : int { RADIUS_ARG = 0, RADIUS_CONTACT = 1, RADIUS_CONTACT_PREV =
 // test is redone in FP64 on the (exactly representable) FP32 coordinates, so
 // the set equals the FP64 reference's on the same inputs.
 template<int MODE>
-__global__ void __launch_bounds__(SBS) k_pairs(Params *Pp, double rc_arg, int radius_sel,
+__global__ void __launch_bounds__(SBS) k_pairs(const __grid_constant__ Params P, double rc_arg, int radius_sel,
                                                int replica, uint2 *out,
                                                unsigned long long out_cap,
                                                unsigned long long *out_count)
 {
     __shared__ PairWalkSmem s_walk[SWARPS];
-    Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     if (replica >= 0 && r != replica) return;
@@ -109,11 +114,11 @@ __global__ void __launch_bounds__(SBS) k_pairs(Params *Pp, double rc_arg, int ra
 
 // Compacts the non-empty slots of one replica's table (replica >= 0) or of
 // all replicas (replica < 0) into (key, count) arrays.
-__global__ void k_contact_compact(Params *Pp, int replica, unsigned long long *out_keys,
+__global__ void k_contact_compact(const __grid_constant__ Params P, int replica, unsigned long long *out_keys,
                                   unsigned int *out_vals, unsigned long long *out_count)
 {
-    const ContactParams &C = Pp->contact;
-    unsigned long long total = (replica < 0 ? (unsigned long long) Pp->n_rep : 1ull) * C.capacity;
+    const ContactParams &C = P.contact;
+    unsigned long long total = (replica < 0 ? (unsigned long long) P.n_rep : 1ull) * C.capacity;
     unsigned long long base = replica < 0 ? 0ull : (unsigned long long) replica * C.capacity;
     for (unsigned long long s = blockIdx.x * (unsigned long long) blockDim.x + threadIdx.x;
          s < total; s += (unsigned long long) gridDim.x * blockDim.x) {
@@ -130,10 +135,9 @@ __global__ void k_contact_compact(Params *Pp, int replica, unsigned long long *o
 // every interaction is counted by exactly one thread; per-block partial sums
 // in FP64 are added on the host in block order (deterministic).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(BS) k_energy(Params *Pp, int r, unsigned mask_arg,
+__global__ void __launch_bounds__(BS) k_energy(const __grid_constant__ Params P, int r, unsigned mask_arg,
                                                double *partials)
 {
-    Params &P = *Pp;
     RepState &st = P.st[r];
     const StepConst &sc = st.sc;
     const unsigned mask = mask_arg & P.enabled;
@@ -262,9 +266,8 @@ __global__ void __launch_bounds__(BS) k_energy(Params *Pp, int r, unsigned mask_
     }
 }
 
-__global__ void k_debug_noise(Params *Pp, int r, long long step, float *out)
+__global__ void k_debug_noise(const __grid_constant__ Params P, int r, long long step, float *out)
 {
-    Params &P = *Pp;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
     f3 z = normal3(P.st[r].seed, (uint32_t) i, step);
@@ -274,9 +277,8 @@ __global__ void k_debug_noise(Params *Pp, int r, long long step, float *out)
 }
 
 // Squared radius of gyration of bead ranges [start, end): one block per range.
-__global__ void k_rg2(Params *Pp, int r, int n_ranges, const int *ranges, double *out)
+__global__ void k_rg2(const __grid_constant__ Params P, int r, int n_ranges, const int *ranges, double *out)
 {
-    Params &P = *Pp;
     int g = blockIdx.x;
     if (g >= n_ranges) return;
     const float4 *pos = P.pos[P.st[r].parity] + (size_t) r * P.n;

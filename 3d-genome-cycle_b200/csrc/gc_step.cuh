@@ -1,13 +1,13 @@
-// gc_step.cuh -- force evaluation + BAOAB-limit Brownian update, fused.
+// gc_step.cuh -- single-bead force terms, BAOAB-limit Brownian update, per-step
+// reductions and the on-device body of the driver's per-step callback.
 //
 // One thread owns one bead (in cell-sorted order) and GATHERS every term that
-// acts on it (full neighbour walk instead of the reference's half-list
-// scatter, MD/forcefield/neighbor_pairwise_forcefield.hpp:68-84), so there are
-// no force atomics and the result is bit-reproducible run to run.
+// acts on it (instead of the reference's half-list scatter,
+// MD/forcefield/bonded_pairwise_forcefield.hpp:78-93), so there are no force
+// atomics and the result is bit-reproducible run to run.
 #pragma once
 
 #include "gc_kernels.cuh"
-#include "gc_pairwalk.cuh"
 
 namespace gc {
 
@@ -19,55 +19,76 @@ enum StepMode : int {
 // ---------------------------------------------------------------------------
 // FP64 context -> FP32 step constants (one thread, once per step per replica)
 // ---------------------------------------------------------------------------
-__device__ inline void refresh_consts(const Params &P, RepState &st)
+// The constants are independent of one another, so the finalize kernels spread
+// the items over the lanes of a warp (FP64 divisions are slow in one thread).
+__device__ inline void refresh_consts_item(const Params &P, RepState &st, int item)
 {
     StepConst &c = st.sc;
-    {
+    if (item == 0) {
         double s = P.pair.scale_by_core ? st.core_scale : 1.0;
         PairCoef pc = make_pair_coef(P.pair.eps_a, P.pair.sigma_a, P.pair.eps_b, P.pair.sigma_b, s,
                                      P.pair.mode == PAIR_NONE ? PAIR_PLAIN : P.pair.mode);
         c.kA2 = pc.kA2; c.kB2 = pc.kB2; c.cA = pc.cA; c.cB = pc.cB;
         c.eA = pc.eA; c.eB = pc.eB; c.rc2 = pc.rc2;
-    }
-    if (P.wall.term >= 0) {
-        double s = P.wall.scale_by_core ? st.core_scale : 1.0;
-        // inward soft cores use HALF diameters
-        // (SIM/stage_interphase/simulation_driver_forcefield.cpp:214-221)
-        PairCoef wc = make_pair_coef(P.wall.eps_a, P.wall.sigma_a * 0.5, P.wall.eps_b,
-                                     P.wall.sigma_b * 0.5, s, PAIR_AB);
-        c.w_kA2 = wc.kA2; c.w_kB2 = wc.kB2; c.w_cA = wc.cA; c.w_cB = wc.cB;
-        c.w_eA = wc.eA; c.w_eB = wc.eB;
-        for (int k = 0; k < 3; k++) {
+    } else if (item == 1) {
+        if (P.wall.term >= 0) {
+            double s = P.wall.scale_by_core ? st.core_scale : 1.0;
+            // inward soft cores use HALF diameters
+            // (SIM/stage_interphase/simulation_driver_forcefield.cpp:214-221)
+            PairCoef wc = make_pair_coef(P.wall.eps_a, P.wall.sigma_a * 0.5, P.wall.eps_b,
+                                         P.wall.sigma_b * 0.5, s, PAIR_AB);
+            c.w_kA2 = wc.kA2; c.w_kB2 = wc.kB2; c.w_cA = wc.cA; c.w_cB = wc.cB;
+            c.w_eA = wc.eA; c.w_eB = wc.eB;
+            c.wall_a = (float) P.wall.wall_a;
+            c.wall_b = (float) P.wall.wall_b;
+            c.wall_K = (float) P.wall.outward_spring;
+        }
+    } else if (item < 5) {
+        if (P.wall.term >= 0) {
+            const int k = item - 2;
             c.qd[k] = 1.0 / (st.semiaxes[k] * st.semiaxes[k]);
             c.q[k] = (float) c.qd[k];
         }
-        c.wall_a = (float) P.wall.wall_a;
-        c.wall_b = (float) P.wall.wall_b;
-        c.wall_K = (float) P.wall.outward_spring;
+    } else if (item == 5) {
+        if (P.well.term >= 0) {
+            c.well_eps = (float) P.well.eps;
+            c.well_k2 = (float) (1.0 / (P.well.decay * P.well.decay));
+            c.well_cut2 = (float) (P.well.cutoff * P.well.cutoff);
+        }
+    } else if (item >= 8 && item < 8 + GC_MAX_BOND_TERMS) {
+        const int b = item - 8;
+        if (b < P.n_bond_terms) {
+            const BondTerm &bt = P.bonds[b];
+            double s = bt.scale ? st.bond_scale : 1.0;
+            double is2 = 1.0 / (s * s);
+            c.bK_a[b] = (float) (bt.K_a * is2);
+            c.bK_b[b] = (float) (bt.K_b * is2);
+            c.bl_a[b] = (float) (bt.l_a * s);
+            c.bl_b[b] = (float) (bt.l_b * s);
+        }
+    } else if (item >= 16 && item < 16 + GC_MAX_TRIPLE_TERMS) {
+        const int t = item - 16;
+        if (t < P.n_triple_terms) c.tE[t] = (float) P.triples[t].energy;
+    } else if (item >= 20 && item < 20 + GC_MAX_SOURCES) {
+        const int k = item - 20;
+        if (k < P.n_sources) {
+            for (int d = 0; d < 3; d++) c.src_pt[k][d] = (float) P.sources[k].point[d];
+            c.src_p0[k] = (float) P.sources[k].p0;
+            c.src_p1[k] = (float) P.sources[k].p1;
+        }
+    } else if (item >= 24 && item < 24 + GC_MAX_POLES) {
+        const int k = item - 24;
+        if (k < P.n_poles) {
+            for (int d = 0; d < 3; d++) c.pole[k][d] = (float) P.poles[k][d];
+        }
     }
-    for (int b = 0; b < P.n_bond_terms; b++) {
-        const BondTerm &bt = P.bonds[b];
-        double s = bt.scale ? st.bond_scale : 1.0;
-        double is2 = 1.0 / (s * s);
-        c.bK_a[b] = (float) (bt.K_a * is2);
-        c.bK_b[b] = (float) (bt.K_b * is2);
-        c.bl_a[b] = (float) (bt.l_a * s);
-        c.bl_b[b] = (float) (bt.l_b * s);
-    }
-    for (int t = 0; t < P.n_triple_terms; t++) c.tE[t] = (float) P.triples[t].energy;
-    for (int k = 0; k < P.n_sources; k++) {
-        for (int d = 0; d < 3; d++) c.src_pt[k][d] = (float) P.sources[k].point[d];
-        c.src_p0[k] = (float) P.sources[k].p0;
-        c.src_p1[k] = (float) P.sources[k].p1;
-    }
-    for (int k = 0; k < P.n_poles; k++) {
-        for (int d = 0; d < 3; d++) c.pole[k][d] = (float) P.poles[k][d];
-    }
-    if (P.well.term >= 0) {
-        c.well_eps = (float) P.well.eps;
-        c.well_k2 = (float) (1.0 / (P.well.decay * P.well.decay));
-        c.well_cut2 = (float) (P.well.cutoff * P.well.cutoff);
-    }
+}
+static_assert(8 + GC_MAX_BOND_TERMS <= 16 && 16 + GC_MAX_TRIPLE_TERMS <= 20 &&
+              20 + GC_MAX_SOURCES <= 24 && 24 + GC_MAX_POLES <= 32, "item layout of refresh_consts");
+
+__device__ inline void refresh_consts(const Params &P, RepState &st)
+{
+    for (int item = 0; item < 32; item++) refresh_consts_item(P, st, item);
 }
 
 // ---------------------------------------------------------------------------
@@ -77,8 +98,7 @@ struct WallAcc {
     float ax, ay, az, reaction;
 };
 
-// PAIRS = false leaves the nonbonded soft cores to pair_force_group().
-template<bool PAIRS>
+// Single-bead terms only: the nonbonded soft cores come from k_pair_cells.
 __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, int r, int t,
                                          int idx, float4 self4, float2 abi, unsigned mask,
                                          WallAcc &wacc)
@@ -88,44 +108,6 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
     const int par = st.parity;
     const f3 self = make_f3(self4);
     f3 F = {0.0f, 0.0f, 0.0f};
-
-    // ---- nonbonded soft cores over the neighbouring cell rows -------------
-    if (PAIRS && P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u)) {
-        PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
-        const bool plain = P.pair.mode == PAIR_PLAIN;
-        const float4 *__restrict__ sp = P.spos[par] + ro;
-        const float2 *__restrict__ sab = P.sab + ro;
-        const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
-        const int dx = st.dims[0], dy = st.dims[1], dz = st.dims[2];
-        const int M = P.cells_per_cut;
-        int c = P.scell[ro + t];
-        int cx = c % dx, cy = (c / dx) % dy, cz = c / (dx * dy);
-        int x0 = max(cx - M, 0), x1 = min(cx + M, dx - 1);
-        for (int z = max(cz - M, 0); z <= min(cz + M, dz - 1); z++) {
-            for (int y = max(cy - M, 0); y <= min(cy + M, dy - 1); y++) {
-                int row = dx * (y + dy * z);
-                int lo = start[row + x0], hi = start[row + x1 + 1];
-                for (int j = lo; j < hi; j++) {
-                    float4 q = __ldg(&sp[j]);
-                    f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
-                    float r2 = dot(d, d);
-                    if (r2 < pc.rc2) {
-                        // the bead itself has d = 0 and contributes exactly 0
-                        float a = 1.0f, b = 0.0f;
-                        if (!plain) {
-                            float2 abj = __ldg(&sab[j]);
-                            a = 0.5f * (abi.x + abj.x);
-                            b = 0.5f * (abi.y + abj.y);
-                        }
-                        float fac = pair_force_factor(pc, a, b, r2);
-                        F.x = fmaf(fac, d.x, F.x);
-                        F.y = fmaf(fac, d.y, F.y);
-                        F.z = fmaf(fac, d.z, F.z);
-                    }
-                }
-            }
-        }
-    }
 
     const float4 *__restrict__ pos = P.pos[par] + ro;   // original order
     const int flags = P.flags[idx];
@@ -283,16 +265,17 @@ __device__ __forceinline__ void red_init(StepRed &s)
     s.bad = false;
 }
 
-// Reduce over the block, push one set of atomics per block, take a ticket.
-// Returns true in every thread of the LAST block of this replica.
+// Reduce over the block and push one set of atomics per block.  The per-step
+// scalars are consumed by k_finalize_*, a separate one-warp launch: the kernel
+// boundary orders it after every block, so no fence/ticket is needed here.
 template<int NT>
-__device__ __forceinline__ bool block_reduce_commit(RepState &st, StepRed &s, bool with_wall,
+__device__ __forceinline__ void block_reduce_commit(RepState &st, StepRed &s, bool with_wall,
                                                     bool with_geom, bool with_dt)
 {
     constexpr int NW = NT / 32;
     __shared__ float sh_f[NW][8];
     __shared__ long long sh_l[NW][4];
-    __shared__ int sh_bad, sh_last;
+    __shared__ int sh_bad;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) sh_bad = 0;
 
@@ -339,13 +322,7 @@ __device__ __forceinline__ bool block_reduce_commit(RepState &st, StepRed &s, bo
             if (q[3]) atomicAdd((unsigned long long *) &st.reaction_fx, (unsigned long long) q[3]);
         }
         if (sh_bad) atomicExch(&st.error, 1);
-        __threadfence();
-        unsigned int prev = atomicAdd(&st.ticket, 1u);
-        sh_last = prev == gridDim.x - 1;
-        if (sh_last) __threadfence();
     }
-    __syncthreads();
-    return sh_last != 0;
 }
 
 // Wall statistics of the force pass just finished: fixed point -> double.
@@ -413,16 +390,13 @@ __device__ inline void finalize_step(const Params &P, RepState &st, double dt_us
         st.bbox_max[k] = (int) 0x80000000;
     }
     st.dtmin_bits = 0x7f800000u;
-    st.ticket = 0u;
     st.cell_cursor = 0;
-    refresh_consts(P, st);
 }
 
 // ---------------------------------------------------------------------------
 // BAOAB-limit update of one bead
 //   MD/simulation/detail/brownian_simulator.hpp:61-75:
 //     x += mu dt F;  x += (W_n + W_{n-1}) / 2;  W = sqrt(2 kT mu dt) N(0,1)^3
-//   W_{n-1} is REGENERATED from the counter-based stream instead of stored.
 //   The two increments are summed first so x is rounded once in FP32.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ f3 bead_noise(const Params &P, const RepState &st, int r, int idx,
@@ -437,8 +411,7 @@ __device__ __forceinline__ f3 bead_noise(const Params &P, const RepState &st, in
 }
 
 __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &st, int r, int t,
-                                               int idx, float4 self4, f3 F, float dt,
-                                               float dt_prev, StepRed &red)
+                                               int idx, float4 self4, f3 F, float dt, StepRed &red)
 {
     const size_t ro = (size_t) r * P.n;
     const int par = st.parity;
@@ -447,9 +420,13 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
     float mudt = dt * mu;
     float sigma = sqrtf(2.0f * P.kT * mudt);
     f3 W = sigma * bead_noise(P, st, r, idx, n);
+    // W_{n-1} is REGENERATED from the counter-based stream instead of being kept
+    // in memory as the reference does (brownian_simulator.hpp:72-74, 83): a stored
+    // copy costs a scattered 16-byte read-modify-write per bead, measured at 2.6x
+    // the whole kernel's time (profiles/r1_notes.md)
     f3 Wp = {0.0f, 0.0f, 0.0f};
     if (n > 1) {
-        float sigma_p = sqrtf(2.0f * P.kT * dt_prev * mu);
+        float sigma_p = sqrtf(2.0f * P.kT * (float) st.dt_last * mu);
         Wp = sigma_p * bead_noise(P, st, r, idx, n - 1);
     }
     float4 x;
@@ -458,12 +435,15 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
     x.z = self4.z + fmaf(mudt, F.z, 0.5f * (W.z + Wp.z));
     x.w = 0.0f;
     P.pos[par ^ 1][ro + idx] = x;
-    x.w = self4.w;
-    P.spos[par ^ 1][ro + t] = x;
-
-    float4 ref = P.sref[ro + t];
-    float ex = x.x - ref.x, ey = x.y - ref.y, ez = x.z - ref.z;
-    red.disp2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+    if (P.skin > 0.0f) {
+        // cells may be reused: keep the sorted copy current and track the largest
+        // displacement since the rebuild (neighbor_list.hpp:129-158)
+        x.w = self4.w;
+        P.spos[par ^ 1][ro + t] = x;
+        float4 ref = P.sref[ro + t];
+        float ex = x.x - ref.x, ey = x.y - ref.y, ez = x.z - ref.z;
+        red.disp2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+    }   // skin == 0: every step re-bins from pos, nothing else reads these
     red.lo[0] = red.hi[0] = x.x;
     red.lo[1] = red.hi[1] = x.y;
     red.lo[2] = red.hi[2] = x.z;
@@ -483,159 +463,9 @@ __device__ __forceinline__ float solve_timestep(float spacestep, float mu, float
     return 2.0f * c / (b + sqrtf(fmaf(b, b, 4.0f * a * c)));
 }
 
-// ---------------------------------------------------------------------------
-// step kernels
-// ---------------------------------------------------------------------------
-constexpr int SBS = 256;                 // threads per block of k_step
-constexpr int SWARPS = SBS / 32;         // warps per block
-constexpr int SBEADS = 32;               // beads per block (= one warp in phase 2)
-constexpr int SPERWARP = SBEADS / SWARPS; // beads each warp walks in phase 1
-static_assert(SBEADS == 32, "phase 2 of k_step is written for exactly one warp");
-
-// Single-warp variant of block_reduce_commit (phase 2 of k_step runs on warp 0).
-__device__ __forceinline__ bool warp_reduce_commit(RepState &st, StepRed &s, bool with_wall,
-                                                   bool with_geom, bool with_dt)
-{
-    const int lane = threadIdx.x & 31;
-    float v[8];
-    for (int k = 0; k < 3; k++) { v[k] = warp_min(s.lo[k]); v[3 + k] = warp_max(s.hi[k]); }
-    v[6] = warp_max(s.disp2 != s.disp2 ? INFINITY : s.disp2);
-    bool nan_disp = __any_sync(0xffffffffu, s.disp2 != s.disp2);
-    v[7] = warp_min(s.dtmin);
-    long long q[4];
-    q[0] = warp_sum(__double2ll_rn((double) s.w.ax * GC_FX_SCALE));
-    q[1] = warp_sum(__double2ll_rn((double) s.w.ay * GC_FX_SCALE));
-    q[2] = warp_sum(__double2ll_rn((double) s.w.az * GC_FX_SCALE));
-    q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
-    bool bad = __any_sync(0xffffffffu, s.bad) || nan_disp;
-    int last = 0;
-    if (lane == 0) {
-        if (with_geom) {
-            for (int k = 0; k < 3; k++) {
-                atomicMin(&st.bbox_min[k], float_to_ordered(v[k]));
-                atomicMax(&st.bbox_max[k], float_to_ordered(v[3 + k]));
-            }
-            atomicMax(&st.maxdisp2_bits, __float_as_uint(v[6]));
-        }
-        if (with_dt) atomicMin(&st.dtmin_bits, __float_as_uint(v[7]));
-        if (with_wall) {
-            for (int k = 0; k < 3; k++) {
-                if (q[k]) atomicAdd((unsigned long long *) &st.axial_fx[k], (unsigned long long) q[k]);
-            }
-            if (q[3]) atomicAdd((unsigned long long *) &st.reaction_fx, (unsigned long long) q[3]);
-        }
-        if (bad) atomicExch(&st.error, 1);
-        __threadfence();
-        unsigned int prev = atomicAdd(&st.ticket, 1u);
-        last = prev == gridDim.x - 1;
-        if (last) __threadfence();
-    }
-    return __shfl_sync(0xffffffffu, last, 0) != 0;
-}
-
-// Phase 1: every warp walks the neighbour cells of SPERWARP beads, one after
-// the other, and evaluates the soft cores on compacted hits.  Phase 2: warp 0
-// owns the block's 32 beads, one lane each: bonded / wall / tether / source
-// terms, noise, update, reductions, and (last block only) the per-step callback.
-template<int MODE>
-__global__ void __launch_bounds__(SBS) k_step(Params *Pp, unsigned mask_arg, int use_enabled)
-{
-    __shared__ PairWalkSmem s_walk[SWARPS];
-    __shared__ float4 s_force[SBEADS];
-
-    Params &P = *Pp;
-    const int r = blockIdx.y;
-    RepState &st = P.st[r];
-    const StepConst &sc = st.sc;
-    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    const size_t ro = (size_t) r * P.n;
-
-    // ---- phase 1 ----------------------------------------------------------
-    {
-        const int lane = threadIdx.x & 31;
-        const int warp = threadIdx.x >> 5;
-        const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
-        const PairCoef pc = {sc.kA2, sc.kB2, sc.cA, sc.cB, sc.eA, sc.eB, sc.rc2};
-        const bool plain = P.pair.mode == PAIR_PLAIN;
-        const float2 *__restrict__ sab = P.sab + ro;
-        for (int b = 0; b < SPERWARP; b++) {
-            const int slot = warp * SPERWARP + b;
-            const int t = blockIdx.x * SBEADS + slot;
-            float fx = 0.0f, fy = 0.0f, fz = 0.0f;
-            if (t < P.n && pair_on) {                     // warp-uniform
-                const float4 self4 = P.spos[st.parity][ro + t];
-                const float2 abi = sab[t];
-                pair_walk<false, false>(P, st, r, t, self4, pc.rc2, s_walk[warp], lane,
-                                        [&](PairHit h) {
-                    // the bead itself has d = 0 and contributes exactly 0
-                    float a = 1.0f, bb = 0.0f;
-                    if (!plain) {
-                        float2 abj = __ldg(&sab[h.j]);
-                        a = 0.5f * (abi.x + abj.x);
-                        bb = 0.5f * (abi.y + abj.y);
-                    }
-                    float r2 = fmaf(h.dx, h.dx, fmaf(h.dy, h.dy, h.dz * h.dz));
-                    float fac = pair_force_factor(pc, a, bb, r2);
-                    fx = fmaf(fac, h.dx, fx);
-                    fy = fmaf(fac, h.dy, fy);
-                    fz = fmaf(fac, h.dz, fz);
-                });
-                fx = warp_sum_f(fx);
-                fy = warp_sum_f(fy);
-                fz = warp_sum_f(fz);
-            }
-            if (lane == 0) s_force[slot] = make_float4(fx, fy, fz, 0.0f);
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x >= 32) return;
-
-    // ---- phase 2 (warp 0) -------------------------------------------------
-    const int t = blockIdx.x * SBEADS + threadIdx.x;
-    StepRed red;
-    red_init(red);
-    if (t < P.n) {
-        float4 self4 = P.spos[st.parity][ro + t];
-        int idx = __float_as_int(self4.w);
-        float2 abi = P.sab[ro + t];
-        f3 F = bead_force<false>(P, st, r, t, idx, self4, abi, mask, red.w);
-        float4 fp = s_force[threadIdx.x];
-        F.x += fp.x;
-        F.y += fp.y;
-        F.z += fp.z;
-        if (MODE == STEP_FORCE) {
-            P.force[ro + idx] = make_float4(F.x, F.y, F.z, 0.0f);
-            if (P.spacestep != 0.0f) {
-                red.dtmin = solve_timestep(P.spacestep, P.mob[idx], dot(F, F), P.kT, P.dt);
-            }
-            red.bad = !(fabsf(F.x) < INFINITY && fabsf(F.y) < INFINITY && fabsf(F.z) < INFINITY);
-        } else {
-            integrate_bead(P, st, r, t, idx, self4, F, P.dt, P.dt, red);
-        }
-    }
-
-    bool last = warp_reduce_commit(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
-    if (last && threadIdx.x == 0) {
-        finalize_stats(st);
-        if (MODE == STEP_FUSED) {
-            finalize_step(P, st, P.dt_cfg);
-        } else {
-            float dtc = P.dt;
-            if (P.spacestep != 0.0f) {
-                dtc = fminf(dtc, __uint_as_float(*(volatile unsigned int *) &st.dtmin_bits));
-            }
-            st.sc.dt_cur = dtc;
-            st.dtmin_bits = 0x7f800000u;
-            st.ticket = 0u;
-            st.cell_cursor = 0;
-        }
-    }
-}
-
 // Second half of an adaptive step: update with the globally reduced dt.
-__global__ void __launch_bounds__(BS) k_integrate(Params *Pp)
+__global__ void __launch_bounds__(BS) k_integrate(const __grid_constant__ Params P)
 {
-    Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const int t = blockIdx.x * BS + threadIdx.x;
@@ -649,16 +479,74 @@ __global__ void __launch_bounds__(BS) k_integrate(Params *Pp)
         int idx = __float_as_int(self4.w);
         float4 F4 = P.force[ro + idx];
         f3 F = {F4.x, F4.y, F4.z};
-        integrate_bead(P, st, r, t, idx, self4, F, dt, (float) st.dt_last, red);
+        integrate_bead(P, st, r, t, idx, self4, F, dt, red);
     }
-    bool last = block_reduce_commit<BS>(st, red, false, true, false);
-    if (last && threadIdx.x == 0) finalize_step(P, st, (double) dt);
+    block_reduce_commit<BS>(st, red, false, true, false);
+}
+
+// ---------------------------------------------------------------------------
+// per-step epilogues: one thread per replica, launched right after the kernel
+// whose reductions they consume
+// ---------------------------------------------------------------------------
+// One warp per replica: the RepState is staged in shared memory (coalesced copy
+// in, serial FP64 bookkeeping by lane 0, coalesced copy out) instead of ~100
+// dependent global round trips.
+__device__ __forceinline__ void repstate_load(RepState &dst, const RepState &src, int lane)
+{
+    const int *s = reinterpret_cast<const int *>(&src);
+    int *d = reinterpret_cast<int *>(&dst);
+    for (int k = lane; k < (int) (sizeof(RepState) / sizeof(int)); k += 32) d[k] = s[k];
+    __syncwarp();
+}
+__device__ __forceinline__ void repstate_store(RepState &dst, const RepState &src, int lane)
+{
+    __syncwarp();
+    const int *s = reinterpret_cast<const int *>(&src);
+    int *d = reinterpret_cast<int *>(&dst);
+    for (int k = lane; k < (int) (sizeof(RepState) / sizeof(int)); k += 32) d[k] = s[k];
+}
+static_assert(sizeof(RepState) % sizeof(int) == 0, "RepState is copied word by word");
+
+// after k_finish<STEP_FUSED> (fixed dt) or k_integrate (adaptive dt)
+__global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Params P, int adaptive)
+{
+    __shared__ RepState s;
+    const int r = blockIdx.x, lane = threadIdx.x;
+    repstate_load(s, P.st[r], lane);
+    if (lane == 0) {
+        if (adaptive) {
+            finalize_step(P, s, (double) s.sc.dt_cur);
+        } else {
+            finalize_stats(s);
+            finalize_step(P, s, P.dt_cfg);
+        }
+    }
+    __syncwarp();
+    refresh_consts_item(P, s, lane);       // constants of the next step, one item per lane
+    repstate_store(P.st[r], s, lane);
+}
+
+// after k_finish<STEP_FORCE>: wall statistics and the adaptive time step
+// (MD/simulation/detail/brownian_timestepper.hpp:109-136: global minimum)
+__global__ void __launch_bounds__(32) k_finalize_force(const __grid_constant__ Params P)
+{
+    __shared__ RepState s;
+    const int r = blockIdx.x, lane = threadIdx.x;
+    repstate_load(s, P.st[r], lane);
+    if (lane == 0) {
+        finalize_stats(s);
+        float dtc = P.dt;
+        if (P.spacestep != 0.0f) dtc = fminf(dtc, __uint_as_float(s.dtmin_bits));
+        s.sc.dt_cur = dtc;
+        s.dtmin_bits = 0x7f800000u;
+        s.cell_cursor = 0;
+    }
+    repstate_store(P.st[r], s, lane);
 }
 
 // radius_override > 0 forces the list radius (gc_neighbor_pairs).
-__global__ void k_plan(Params *Pp, double radius_override)
+__global__ void k_plan(const __grid_constant__ Params P, double radius_override)
 {
-    Params &P = *Pp;
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];

@@ -14,9 +14,8 @@ namespace gc {
 // Single-bead terms + update (or force output), one thread per sorted slot, full
 // occupancy; consumes the nonbonded force of k_pair_tile.
 template<int MODE>
-__global__ void __launch_bounds__(BS) k_finish(Params *Pp, unsigned mask_arg, int use_enabled)
+__global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P, unsigned mask_arg, int use_enabled)
 {
-    Params &P = *Pp;
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
@@ -29,7 +28,7 @@ __global__ void __launch_bounds__(BS) k_finish(Params *Pp, unsigned mask_arg, in
         const float4 self4 = P.spos[st.parity][ro + t];
         const int idx = __float_as_int(self4.w);
         const float2 abi = P.sab[ro + t];
-        f3 F = bead_force<false>(P, st, r, t, idx, self4, abi, mask, red.w);
+        f3 F = bead_force(P, st, r, t, idx, self4, abi, mask, red.w);
         const float4 fp = P.pforce[ro + t];
         F.x += fp.x;
         F.y += fp.y;
@@ -41,26 +40,11 @@ __global__ void __launch_bounds__(BS) k_finish(Params *Pp, unsigned mask_arg, in
             }
             red.bad = !(fabsf(F.x) < INFINITY && fabsf(F.y) < INFINITY && fabsf(F.z) < INFINITY);
         } else {
-            integrate_bead(P, st, r, t, idx, self4, F, P.dt, P.dt, red);
+            integrate_bead(P, st, r, t, idx, self4, F, P.dt, red);
         }
     }
 
-    const bool last = block_reduce_commit<BS>(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
-    if (last && threadIdx.x == 0) {
-        finalize_stats(st);
-        if (MODE == STEP_FUSED) {
-            finalize_step(P, st, P.dt_cfg);
-        } else {
-            float dtc = P.dt;
-            if (P.spacestep != 0.0f) {
-                dtc = fminf(dtc, __uint_as_float(*(volatile unsigned int *) &st.dtmin_bits));
-            }
-            st.sc.dt_cur = dtc;
-            st.dtmin_bits = 0x7f800000u;
-            st.ticket = 0u;
-            st.cell_cursor = 0;
-        }
-    }
+    block_reduce_commit<BS>(st, red, true, MODE == STEP_FUSED, MODE == STEP_FORCE);
 }
 
 } // namespace gc

@@ -3,12 +3,13 @@
 // Layout in HBM (R replicas x N beads, one context per GPU):
 //   pos [2][R][N] float4   positions in ORIGINAL bead order, ping-pong by step parity
 //   spos[2][R][N] float4   positions in CELL-SORTED order (w = original index bits)
-//   sref   [R][N] float4   sorted positions at the last rebuild (skin check)
-//   sidx / scell / slot_of [R][N] int32  sorted<->original maps, cell of each slot
+//   sref   [R][N] float4   sorted positions at the last rebuild (skin > 0 only)
+//   scell  [R][N] int32    cell of each sorted slot (query kernels)
 //   sab    [R][N] float2   (a, b) factors gathered into sorted order
 //   cell_count / cell_start [R][ncell_max(+1)] int32
 //   cell_list [R][N] int4   non-empty cells (the pair kernel's work queue)
 //   force  [R][N] float4   only for the adaptive stepper / gc_compute_force
+//   pforce [R][N] float4   nonbonded force in sorted order (pair kernel -> k_finish)
 //   st     [R]    RepState per-replica scalars (schedule, wall, reductions)
 // Bead attributes and bonded topology are shared by all replicas.
 #pragma once
@@ -130,7 +131,7 @@ struct RepState {
     unsigned int maxdisp2_bits;    // max |x - x_ref|^2 since rebuild (float bits)
     unsigned int dtmin_bits;       // adaptive dt candidate (float bits)
     int bbox_min[3], bbox_max[3];  // order-preserving int encoding of floats
-    unsigned int ticket;
+    int scan_ticket;               // block order of the chained cell scan
     int n_used_cells;              // entries of Params::cell_list (non-empty cells)
     int cell_cursor;               // work-queue head of the pair kernel, reset every step
     // --- cell grid ---
@@ -172,12 +173,14 @@ struct Params {
     float4 *pos[2];
     float4 *spos[2];
     float4 *sref;
-    int *sidx, *scell, *slot_of;
+    int *scell;
     float2 *sab;
     int *cell_count, *cell_start, *members, *cell_of;
+    unsigned long long *scan_status;   // [R][scan_blocks] look-back words of k_scan
+    int scan_blocks;               // ceil(ncell_max / SCAN_TILE)
     int4 *cell_list;               // [R][N] non-empty cells {cell, first slot, beads, 0}
     float4 *force;                 // total force, ORIGINAL order (adaptive stepper, gc_compute_force)
-    float4 *pforce;                // nonbonded force, SORTED order (k_pair_tile -> k_finish)
+    float4 *pforce;                // nonbonded force, SORTED order (k_pair_cells -> k_finish)
     RepState *st;
     const float *noise;            // injected normals [R][steps][N][3] or null
     long long noise_steps;         // steps covered by `noise`
@@ -195,5 +198,7 @@ struct Params {
     SourceTerm sources[GC_MAX_SOURCES];
     double poles[GC_MAX_POLES][3];
 };
+
+static_assert(sizeof(Params) <= 4000, "Params is passed by value as a kernel argument");
 
 } // namespace gc
