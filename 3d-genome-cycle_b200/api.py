@@ -96,6 +96,11 @@ SYMBOLS = [
     ("gc_contacts_fetch", C.c_int, [_P, C.c_int32, C.POINTER(C.c_uint32), C.c_size_t,
                                     C.POINTER(C.c_size_t)]),
     ("gc_contacts_clear", C.c_int, [_P]),
+    ("gc_contacts_reduce_device", C.c_int, [_P, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_size_t)]),
+    ("gc_contacts_merge_device", C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_size_t,
+                                           C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                           C.POINTER(C.c_size_t)]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
@@ -153,6 +158,14 @@ def _i(a):
 
 def _ptr(a, typ):
     return a.ctypes.data_as(C.POINTER(typ))
+
+
+class _DeviceArray:
+    """Raw device pointer -> __cuda_array_interface__ (zero-copy view for torch)."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr,
+                                         "data": (int(ptr), False), "version": 3}
 
 
 class System:
@@ -339,6 +352,36 @@ class System:
 
     def contacts_clear(self):
         self._ck(self.lib.gc_contacts_clear(self._h))
+
+    def _device_pairs(self, k, v, n, device):
+        """(keys int64[n], counts int32[n]) torch tensors COPIED from context-owned buffers."""
+        import torch
+        dev = torch.device("cuda", device)
+        if n.value == 0:
+            return (torch.empty(0, dtype=torch.int64, device=dev),
+                    torch.empty(0, dtype=torch.int32, device=dev))
+        keys = torch.as_tensor(_DeviceArray(k.value, n.value, "<i8"), device=dev).clone()
+        cnts = torch.as_tensor(_DeviceArray(v.value, n.value, "<i4"), device=dev).clone()
+        return keys, cnts
+
+    def contacts_reduce_device(self, replica=-1, device=0):
+        """Sorted (key = i << 32 | j, count) of one replica, or summed over this
+        context's replicas, as CUDA tensors (for an NCCL gather across ranks)."""
+        k, v, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        self._ck(self.lib.gc_contacts_reduce_device(self._h, replica, C.byref(k), C.byref(v),
+                                                    C.byref(n)))
+        return self._device_pairs(k, v, n, device)
+
+    def contacts_merge_device(self, keys, counts, device=0):
+        """Sort + sum (key, count) CUDA tensors gathered from several ranks."""
+        keys, counts = keys.contiguous(), counts.contiguous()
+        assert keys.dtype.itemsize == 8 and counts.dtype.itemsize == 4 and keys.is_cuda
+        k, v, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        import torch
+        torch.cuda.current_stream(keys.device).synchronize()
+        self._ck(self.lib.gc_contacts_merge_device(self._h, keys.data_ptr(), counts.data_ptr(),
+                                                   keys.numel(), C.byref(k), C.byref(v), C.byref(n)))
+        return self._device_pairs(k, v, n, device)
 
     # ---- observables / misc -----------------------------------------------
     def radius_of_gyration2(self, ranges, replica=0):

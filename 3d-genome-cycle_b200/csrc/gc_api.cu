@@ -72,6 +72,11 @@ struct gc_ctx {
     int tile_grid_x = 1;        // blocks per replica of the pair kernel
 
 
+    // result of the last contact query (sorted keys / counts on the device)
+    unsigned long long *res_keys = nullptr;
+    unsigned int *res_vals = nullptr;
+    size_t res_count = 0;
+
     // per-kernel event timing (gc_profile_*)
     struct ProfKernel {
         std::string name;
@@ -1058,16 +1063,87 @@ int gc_contacts_clear(gc_ctx *ctx)
     });
 }
 
-int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity, size_t *count)
+} // extern "C"
+
+namespace {
+
+void free_contact_result(gc_ctx *ctx)
 {
-    GC_CHECK_CTX(ctx);
-    if (!count || replica < -1 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    dev_free(ctx, ctx->res_keys);
+    dev_free(ctx, ctx->res_vals);
+    ctx->res_keys = nullptr;
+    ctx->res_vals = nullptr;
+    ctx->res_count = 0;
+}
+
+// Sorts (key, count) pairs by key = (i << 32 | j) -- the order contact_map::accumulate
+// produces (SIM/stage_interphase/contact_map.cpp:75-82) -- and, if `reduce`, sums the
+// counts of equal keys (ensemble sum).  Takes ownership of k_in / v_in; the result
+// lives in ctx->res_* until the next contact query.
+int sort_reduce_contacts(gc_ctx *ctx, unsigned long long *k_in, unsigned int *v_in, size_t m,
+                         bool reduce)
+{
+    unsigned long long *k_out = nullptr, *d_runs = nullptr;
+    unsigned int *v_out = nullptr;
+    unsigned char *tmp = nullptr;
+    auto cleanup = [&] {
+        dev_free(ctx, k_in); dev_free(ctx, v_in); dev_free(ctx, k_out); dev_free(ctx, v_out);
+        dev_free(ctx, d_runs); dev_free(ctx, tmp);
+    };
+    free_contact_result(ctx);
+    if (m == 0) { cleanup(); return GC_OK; }
+    if (m > (size_t) INT32_MAX) { cleanup(); return fail(ctx, GC_ERR_CAPACITY, "too many contact keys"); }
+    int rc = dev_alloc(ctx, &k_out, m);
+    if (!rc) rc = dev_alloc(ctx, &v_out, m);
+    if (!rc) rc = dev_alloc(ctx, &d_runs, 1);
+    if (rc) { cleanup(); return rc; }
+    size_t tmp_bytes = 0, tmp2 = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
+                                    ctx->stream);
+    if (reduce) {
+        cub::DeviceReduce::ReduceByKey(nullptr, tmp2, k_out, k_in, v_out, v_in, d_runs, cub::Sum(),
+                                       (int) m, ctx->stream);
+    }
+    tmp_bytes = std::max(tmp_bytes, tmp2);
+    rc = dev_alloc(ctx, &tmp, tmp_bytes);
+    if (rc) { cleanup(); return rc; }
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
+                                    ctx->stream);
+    ctx->launches += 8;
+    size_t n_out = m;
+    if (reduce) {
+        cub::DeviceReduce::ReduceByKey(tmp, tmp_bytes, k_out, k_in, v_out, v_in, d_runs, cub::Sum(),
+                                       (int) m, ctx->stream);
+        ctx->launches += 2;
+        unsigned long long runs = 0;
+        cudaError_t e = cudaMemcpyAsync(&runs, d_runs, sizeof runs, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) {
+            cleanup();
+            return fail(ctx, GC_ERR_CUDA, "contact reduce: %s", cudaGetErrorString(e));
+        }
+        n_out = (size_t) runs;
+        std::swap(k_in, k_out);
+        std::swap(v_in, v_out);
+    }
+    ctx->res_keys = k_out;
+    ctx->res_vals = v_out;
+    ctx->res_count = n_out;
+    k_out = nullptr;
+    v_out = nullptr;
+    cudaStreamSynchronize(ctx->stream);
+    cleanup();
+    return GC_OK;
+}
+
+// table slots of one replica (or all) -> sorted (and, for all, summed) device arrays
+int reduce_contact_tables(gc_ctx *ctx, int replica)
+{
     ContactParams &C = ctx->hp.contact;
-    *count = 0;
+    free_contact_result(ctx);
     if (!C.keys) return GC_OK;
     int rc = finalize(ctx);
     if (rc) return rc;
-
     std::vector<unsigned int> used((size_t) ctx->n_rep);
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     GC_CUDA(ctx, cudaMemcpy(used.data(), C.used, used.size() * sizeof(unsigned int),
@@ -1077,68 +1153,36 @@ int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capaci
         if (replica < 0 || r == replica) m += used[r];
     }
     if (m == 0) return GC_OK;
-
-    unsigned long long *k_in = nullptr, *k_out = nullptr, *k_red = nullptr, *d_runs = nullptr;
-    unsigned int *v_in = nullptr, *v_out = nullptr, *v_red = nullptr;
-    void *tmp = nullptr;
-    auto cleanup = [&] {
-        dev_free(ctx, k_in); dev_free(ctx, k_out); dev_free(ctx, k_red); dev_free(ctx, d_runs);
-        dev_free(ctx, v_in); dev_free(ctx, v_out); dev_free(ctx, v_red);
-        if (tmp) dev_free(ctx, tmp);
-    };
+    unsigned long long *k_in = nullptr;
+    unsigned int *v_in = nullptr;
     rc = dev_alloc(ctx, &k_in, m);
-    if (!rc) rc = dev_alloc(ctx, &k_out, m);
     if (!rc) rc = dev_alloc(ctx, &v_in, m);
-    if (!rc) rc = dev_alloc(ctx, &v_out, m);
-    if (!rc) rc = dev_alloc(ctx, &d_runs, 1);
-    if (rc) { cleanup(); return rc; }
-
+    if (rc) { dev_free(ctx, k_in); dev_free(ctx, v_in); return rc; }
     GC_CUDA(ctx, cudaMemsetAsync(ctx->d_counter, 0, sizeof(unsigned long long), ctx->stream));
     LAUNCH(ctx, k_contact_compact, 148 * 8, 256, ctx->hp, replica, k_in, v_in, ctx->d_counter);
+    return sort_reduce_contacts(ctx, k_in, v_in, m, replica < 0);
+}
 
-    // sort by key = (i << 32 | j): the order contact_map::accumulate produces
-    // (SIM/stage_interphase/contact_map.cpp:75-82)
-    size_t tmp_bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
-                                    ctx->stream);
-    size_t tmp2 = 0;
-    if (replica < 0) {
-        cub::DeviceReduce::ReduceByKey(nullptr, tmp2, k_out, k_in, v_out, v_in, d_runs,
-                                       cub::Sum(), (int) m, ctx->stream);
-    }
-    tmp_bytes = std::max(tmp_bytes, tmp2);
-    {
-        unsigned char *t8 = nullptr;
-        rc = dev_alloc(ctx, &t8, tmp_bytes);
-        if (rc) { cleanup(); return rc; }
-        tmp = t8;
-    }
-    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k_in, k_out, v_in, v_out, (int) m, 0, 64,
-                                    ctx->stream);
-    ctx->launches += 8;
-    size_t n_out = m;
-    const unsigned long long *k_res = k_out;
-    const unsigned int *v_res = v_out;
-    if (replica < 0) {
-        // ensemble sum: equal keys of different replicas are adjacent after the sort
-        cub::DeviceReduce::ReduceByKey(tmp, tmp_bytes, k_out, k_in, v_out, v_in, d_runs, cub::Sum(),
-                                       (int) m, ctx->stream);
-        ctx->launches += 2;
-        unsigned long long runs = 0;
-        GC_CUDA(ctx, cudaMemcpyAsync(&runs, d_runs, sizeof runs, cudaMemcpyDeviceToHost, ctx->stream));
-        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        n_out = (size_t) runs;
-        k_res = k_in;
-        v_res = v_in;
-    }
+} // namespace
+
+extern "C" {
+
+int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity, size_t *count)
+{
+    GC_CHECK_CTX(ctx);
+    if (!count || replica < -1 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    *count = 0;
+    int rc = reduce_contact_tables(ctx, replica);
+    if (rc) return rc;
+    const size_t n_out = ctx->res_count;
     *count = n_out;
-    if (ijv) {
+    if (ijv && n_out) {
         size_t take = std::min(n_out, capacity);
         std::vector<unsigned long long> hk(take);
         std::vector<unsigned int> hv(take);
-        GC_CUDA(ctx, cudaMemcpyAsync(hk.data(), k_res, take * sizeof(unsigned long long),
+        GC_CUDA(ctx, cudaMemcpyAsync(hk.data(), ctx->res_keys, take * sizeof(unsigned long long),
                                      cudaMemcpyDeviceToHost, ctx->stream));
-        GC_CUDA(ctx, cudaMemcpyAsync(hv.data(), v_res, take * sizeof(unsigned int),
+        GC_CUDA(ctx, cudaMemcpyAsync(hv.data(), ctx->res_vals, take * sizeof(unsigned int),
                                      cudaMemcpyDeviceToHost, ctx->stream));
         GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         for (size_t k = 0; k < take; k++) {
@@ -1147,9 +1191,47 @@ int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capaci
             ijv[3 * k + 2] = hv[k];
         }
     }
-    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cleanup();
     if (ijv && n_out > capacity) return fail(ctx, GC_ERR_CAPACITY, "contact buffer too small: %zu", n_out);
+    return GC_OK;
+}
+
+int gc_contacts_reduce_device(gc_ctx *ctx, int32_t replica, uint64_t **keys, uint32_t **counts,
+                              size_t *n)
+{
+    GC_CHECK_CTX(ctx);
+    if (!keys || !counts || !n || replica < -1 || replica >= ctx->n_rep) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    int rc = reduce_contact_tables(ctx, replica);
+    if (rc) return rc;
+    *keys = (uint64_t *) ctx->res_keys;
+    *counts = ctx->res_vals;
+    *n = ctx->res_count;
+    return GC_OK;
+}
+
+int gc_contacts_merge_device(gc_ctx *ctx, const uint64_t *keys_in, const uint32_t *counts_in,
+                             size_t n_in, uint64_t **keys, uint32_t **counts, size_t *n)
+{
+    GC_CHECK_CTX(ctx);
+    if (!keys || !counts || !n || (n_in && (!keys_in || !counts_in))) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    unsigned long long *k_in = nullptr;
+    unsigned int *v_in = nullptr;
+    int rc = dev_alloc(ctx, &k_in, n_in);
+    if (!rc) rc = dev_alloc(ctx, &v_in, n_in);
+    if (rc) { dev_free(ctx, k_in); dev_free(ctx, v_in); return rc; }
+    // the inputs may be the previous result buffers: copy before they are released
+    GC_CUDA(ctx, cudaMemcpyAsync(k_in, keys_in, n_in * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
+                                 ctx->stream));
+    GC_CUDA(ctx, cudaMemcpyAsync(v_in, counts_in, n_in * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
+                                 ctx->stream));
+    rc = sort_reduce_contacts(ctx, k_in, v_in, n_in, true);
+    if (rc) return rc;
+    *keys = (uint64_t *) ctx->res_keys;
+    *counts = ctx->res_vals;
+    *n = ctx->res_count;
     return GC_OK;
 }
 

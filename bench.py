@@ -251,7 +251,9 @@ def run_b200_arm(args):
     R, S, n = args.replicas, args.sim_steps, design.n
     g = gc_b200.System(n, R, local)
     stages.setup_interphase(g, design, cfg)
-    g.set_seeds(np.arange(1, R + 1, dtype=np.uint64) + np.uint64(1000 * rank))
+    ens = gc_b200.ensemble
+    cells = ens.shard_replicas(world * R, world, rank)          # global cell ids of this rank
+    g.set_seeds(ens.replica_seeds(20250001, cells))
 
     x, how = cached_state(design)
     if x is None:
@@ -320,12 +322,26 @@ def run_b200_arm(args):
             for r in range(R):
                 g.set_positions_f32(host[r], r)
             g.run(S, cfg.timestep, restart=False)
-            g.contacts_clear()
+            if k + 1 < args.steps:
+                g.contacts_clear()
             for r in range(R):
                 host[r] = g.get_positions_f32(r)
             c = g.get_context(0)
             energy = g.compute_energy(replica=0) / n
+        # output window: ensemble contact map (device reduce per rank, NCCL gather, device
+        # merge) and observables, inside the timed region
+        t1 = time.perf_counter()
+        keys, counts = g.contacts_reduce_device(-1, local)
+        keys, counts = ens.gather_contacts(keys, counts,
+                                           merge=lambda a, b: g.contacts_merge_device(a, b, local))
+        rg2 = np.stack([g.radius_of_gyration2(design.chains, r) for r in range(R)])
+        obs = torch.tensor(np.concatenate([rg2.sum(axis=0), [float(R)]]), dtype=torch.float64,
+                           device=f"cuda:{local}")
+        obs = ens.reduce_sum(obs).cpu().numpy()
+        ijv = ens.keys_to_ijv(keys, counts) if rank == 0 else None
+        g.contacts_clear()
         barrier()
+        t_reduce = time.perf_counter() - t1
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local}")
         if world > 1:
@@ -335,6 +351,18 @@ def run_b200_arm(args):
                "h2d_bytes_per_step": R * n * 16, "d2h_bytes_per_step": R * n * 16 + 8 * 16 + 8,
                "ms_per_step": dt / args.steps * 1e3, "energy_per_bead": energy,
                "semiaxis_x": c.semiaxes[0]}
+        if rank == 0:
+            updates = S // cfg.contactmap_update_interval
+            ps = ens.contact_probability(ijv, design.chains, updates, world * R, max_s=1000)
+            e2e["ensemble"] = {
+                "cells": world * R, "contact_pairs": int(len(ijv)),
+                "contact_counts": int(ijv[:, 2].sum()) if len(ijv) else 0,
+                "reduce_ms": t_reduce * 1e3,
+                "collective": "nccl all_gather of per-rank (key, count) runs + all_reduce of Rg^2"
+                              if world > 1 else "none (1 rank)",
+                "rg_mean": float(np.sqrt(obs[:-1] / obs[-1]).mean()),
+                "P_s": {str(sep): float(ps[sep]) for sep in (1, 2, 5, 10, 30, 100, 300, 1000)},
+            }
 
     # ---- roofline of the dominant kernel: separate short pass with per-kernel events
     roof = None

@@ -241,6 +241,16 @@ int gc_contacts_update(gc_ctx *ctx);
 int gc_contacts_fetch(gc_ctx *ctx, int32_t replica, uint32_t *ijv, size_t capacity,
                       size_t *count);
 int gc_contacts_clear(gc_ctx *ctx);
+/* The same reduction left ON THE DEVICE for an NCCL gather across GPUs
+   (the reference merges ensembles offline, src/cool.py:80-114): keys = i << 32 | j
+   ascending, counts parallel to them.  The buffers belong to the context and stay
+   valid until its next contact query. */
+int gc_contacts_reduce_device(gc_ctx *ctx, int32_t replica, uint64_t **keys, uint32_t **counts,
+                              size_t *n);
+/* Sorts and sums n_in (key, count) device pairs gathered from several ranks; inputs
+   may alias a previous result of this context. */
+int gc_contacts_merge_device(gc_ctx *ctx, const uint64_t *keys_in, const uint32_t *counts_in,
+                             size_t n_in, uint64_t **keys, uint32_t **counts, size_t *n);
 
 /* ---- observables ------------------------------------------------------- */
 
