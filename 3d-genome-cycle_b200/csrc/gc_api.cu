@@ -1007,19 +1007,25 @@ int gc_set_contact_map(gc_ctx *ctx, double distance, int64_t interval, int32_t s
     GC_CHECK_CTX(ctx);
     if (!(distance >= 0) || interval < 0) return fail(ctx, GC_ERR_INVALID, "bad args");
     ContactParams &C = ctx->hp.contact;
-    size_t cap = table_capacity ? table_capacity : std::max<size_t>(256 * (size_t) ctx->n, 1 << 16);
+    size_t cap = table_capacity ? table_capacity : std::max<size_t>(64 * (size_t) ctx->n, 1 << 16);
     size_t pow2 = 1;
     while (pow2 < cap) pow2 <<= 1;
-    if (!C.keys || C.capacity != pow2) {
+    int slots = 128;
+    if (const char *env = getenv("GC_CONTACT_BUCKET")) slots = std::max(1, atoi(env));
+    while (slots & (slots - 1)) slots++;               // power of two
+    if (!C.keys || C.capacity != pow2 || C.bucket_slots != slots) {
         if (C.keys) dev_free(ctx, C.keys);
         if (C.vals) dev_free(ctx, C.vals);
         if (C.used) dev_free(ctx, C.used);
-        C.keys = nullptr; C.vals = nullptr; C.used = nullptr;
+        if (C.bucket) dev_free(ctx, C.bucket);
+        C.keys = nullptr; C.vals = nullptr; C.used = nullptr; C.bucket = nullptr;
         int rc = dev_alloc(ctx, &C.keys, pow2 * ctx->n_rep, 0xff);
         if (!rc) rc = dev_alloc(ctx, &C.vals, pow2 * ctx->n_rep);
         if (!rc) rc = dev_alloc(ctx, &C.used, (size_t) ctx->n_rep);
+        if (!rc) rc = dev_alloc(ctx, &C.bucket, (size_t) ctx->n_rep * ctx->n * slots, 0xff);
         if (rc) return rc;
         C.capacity = pow2;
+        C.bucket_slots = slots;
     }
     C.base_distance = distance;
     C.interval = interval;
@@ -1053,6 +1059,8 @@ int gc_contacts_clear(gc_ctx *ctx)
     if (!C.keys) return GC_OK;
     GC_CUDA(ctx, cudaMemsetAsync(C.keys, 0xff, C.capacity * ctx->n_rep * sizeof(unsigned long long),
                                  ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(C.bucket, 0xff, (size_t) ctx->n_rep * ctx->n * C.bucket_slots *
+                                                     sizeof(unsigned long long), ctx->stream));
     GC_CUDA(ctx, cudaMemsetAsync(C.vals, 0, C.capacity * ctx->n_rep * sizeof(unsigned int),
                                  ctx->stream));
     GC_CUDA(ctx, cudaMemsetAsync(C.used, 0, ctx->n_rep * sizeof(unsigned int), ctx->stream));

@@ -20,34 +20,52 @@ __device__ __forceinline__ unsigned long long hash64(unsigned long long k)
 }
 
 // contact_map::update's `contacts[{i, j}] += 1`
-// (SIM/stage_interphase/contact_map.cpp:52-58) on an open-addressing table.
-__device__ __forceinline__ void contact_insert(const ContactParams &C, int r, RepState &st,
-                                               unsigned int i, unsigned int j)
+// (SIM/stage_interphase/contact_map.cpp:52-58), i < j.
+__device__ __forceinline__ void contact_insert(const ContactParams &C, int n_beads, int r,
+                                               RepState &st, unsigned int i, unsigned int j)
 {
+    // ---- bead i's private bucket --------------------------------------------------
+    const unsigned int S = (unsigned int) C.bucket_slots;
+    unsigned long long *b = C.bucket + ((size_t) r * n_beads + i) * S;
+    const unsigned int h = (j * 0x9E3779B1u) >> 16;
+    for (unsigned int p = 0; p < S; p++) {
+        unsigned long long *w = b + ((h + p) & (S - 1));
+        unsigned long long cur = *(volatile unsigned long long *) w;
+        if (cur == GC_EMPTY_KEY) {
+            cur = atomicCAS(w, GC_EMPTY_KEY, ((unsigned long long) j << 32) | 1ull);
+            if (cur == GC_EMPTY_KEY) {
+                atomicAdd(&C.used[r], 1u);
+                return;
+            }
+        }
+        if ((unsigned int) (cur >> 32) == j) {
+            atomicAdd(w, 1ull);          // the count lives in the low word
+            return;
+        }
+    }
+    // ---- bucket full: spill table, bounded linear probing ------------------------------
+    if (st.error == 2) return;
     unsigned long long key = ((unsigned long long) i << 32) | j;
     unsigned long long mask = C.capacity - 1;
     unsigned long long *keys = C.keys + (size_t) r * C.capacity;
     unsigned int *vals = C.vals + (size_t) r * C.capacity;
-    unsigned long long h = hash64(key) & mask;
-    // Bounded linear probing: a table that is (nearly) full fails fast with
-    // GC_ERR_CAPACITY instead of degenerating into capacity-long scans.
-    if (st.error == 2) return;
+    unsigned long long hh = hash64(key) & mask;
     for (int probe = 0; probe < GC_MAX_PROBES; probe++) {
-        unsigned long long cur = keys[h];
+        unsigned long long cur = keys[hh];
         if (cur == GC_EMPTY_KEY) {
-            cur = atomicCAS(&keys[h], GC_EMPTY_KEY, key);
+            cur = atomicCAS(&keys[hh], GC_EMPTY_KEY, key);
             if (cur == GC_EMPTY_KEY) {
                 atomicAdd(&C.used[r], 1u);
                 cur = key;
             }
         }
         if (cur == key) {
-            atomicAdd(&vals[h], 1u);
+            atomicAdd(&vals[hh], 1u);
             return;
         }
-        h = (h + 1) & mask;
+        hh = (hh + 1) & mask;
     }
-    atomicExch(&st.error, 2);   // table full
+    atomicExch(&st.error, 2);   // both levels full -> GC_ERR_CAPACITY
 }
 
 constexpr int SBS = 256;                 // threads per block of k_pairs
@@ -103,7 +121,7 @@ __global__ void __launch_bounds__(SBS) k_pairs(const __grid_constant__ Params P,
         }
         if (!in) return;
         if (MODE == PAIRS_CONTACT) {
-            contact_insert(P.contact, r, st, (unsigned) idx, (unsigned) h.j);
+            contact_insert(P.contact, P.n, r, st, (unsigned) idx, (unsigned) h.j);
         } else {
             unsigned long long k = atomicAdd(out_count, 1ull);
             if (k < out_cap) out[k] = make_uint2((unsigned) idx, (unsigned) h.j);
@@ -112,21 +130,32 @@ __global__ void __launch_bounds__(SBS) k_pairs(const __grid_constant__ Params P,
     }
 }
 
-// Compacts the non-empty slots of one replica's table (replica >= 0) or of
-// all replicas (replica < 0) into (key, count) arrays.
-__global__ void k_contact_compact(const __grid_constant__ Params P, int replica, unsigned long long *out_keys,
-                                  unsigned int *out_vals, unsigned long long *out_count)
+// Compacts the stored pairs of one replica (replica >= 0) or of all replicas
+// (replica < 0) into (key = i << 32 | j, count) arrays: buckets first, then spill.
+__global__ void k_contact_compact(const __grid_constant__ Params P, int replica,
+                                  unsigned long long *out_keys, unsigned int *out_vals,
+                                  unsigned long long *out_count)
 {
     const ContactParams &C = P.contact;
-    unsigned long long total = (replica < 0 ? (unsigned long long) P.n_rep : 1ull) * C.capacity;
-    unsigned long long base = replica < 0 ? 0ull : (unsigned long long) replica * C.capacity;
-    for (unsigned long long s = blockIdx.x * (unsigned long long) blockDim.x + threadIdx.x;
-         s < total; s += (unsigned long long) gridDim.x * blockDim.x) {
-        unsigned long long k = C.keys[base + s];
+    const unsigned long long nrep = replica < 0 ? (unsigned long long) P.n_rep : 1ull;
+    const unsigned long long r0 = replica < 0 ? 0ull : (unsigned long long) replica;
+    const unsigned long long per_rep = (unsigned long long) P.n * C.bucket_slots;
+    const unsigned long long stride = (unsigned long long) gridDim.x * blockDim.x;
+    const unsigned long long tid = blockIdx.x * (unsigned long long) blockDim.x + threadIdx.x;
+    for (unsigned long long s = tid; s < nrep * per_rep; s += stride) {
+        const unsigned long long w = C.bucket[r0 * per_rep + s];
+        if (w == GC_EMPTY_KEY) continue;
+        const unsigned long long i = (s % per_rep) / C.bucket_slots;
+        const unsigned long long o = atomicAdd(out_count, 1ull);
+        out_keys[o] = (i << 32) | (w >> 32);
+        out_vals[o] = (unsigned int) w;
+    }
+    for (unsigned long long s = tid; s < nrep * C.capacity; s += stride) {
+        const unsigned long long k = C.keys[r0 * C.capacity + s];
         if (k == GC_EMPTY_KEY) continue;
-        unsigned long long o = atomicAdd(out_count, 1ull);
+        const unsigned long long o = atomicAdd(out_count, 1ull);
         out_keys[o] = k;
-        out_vals[o] = C.vals[base + s];
+        out_vals[o] = C.vals[r0 * C.capacity + s];
     }
 }
 

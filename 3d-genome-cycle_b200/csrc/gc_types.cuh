@@ -76,15 +76,22 @@ struct Schedule {
     double core_init, core_tau, bond_init, bond_tau;
 };
 
+// Contact map (SIM/stage_interphase/contact_map.hpp:11-68).  Every bead i owns a
+// small open-addressing bucket of (j << 32 | count) words for its partners j > i,
+// so all inserts of a home bead land in two cache lines; pairs that do not fit
+// spill into a conventional (i << 32 | j) -> count hash table.
 struct ContactParams {
     double base_distance;
     long long interval;
     int scale_by_core;
     int enabled;
-    unsigned long long *keys; // [R][capacity]
-    unsigned int *vals;       // [R][capacity]
-    unsigned long long capacity; // power of two, per replica
-    unsigned int *used;       // [R] distinct keys inserted
+    unsigned long long *bucket;   // [R][N][bucket_slots]
+    int bucket_slots;             // power of two
+    int pad;
+    unsigned long long *keys;     // spill table [R][capacity]
+    unsigned int *vals;           // [R][capacity]
+    unsigned long long capacity;  // power of two, per replica
+    unsigned int *used;           // [R] distinct pairs stored (buckets + spill)
 };
 
 // Per-bead bonded adjacency (gather form: every bead sums its own terms, no

@@ -230,7 +230,9 @@ int gc_neighbor_pairs(gc_ctx *ctx, int32_t replica, double radius, uint32_t *pai
 /* interval = update cadence in steps inside gc_run (0 = never automatic);
    distance scales with core_scale(t) when scale_by_core is set (interphase
    callback: contact distance = contactmap_distance * core_scale);
-   table_capacity = hash slots per replica (0 = default). */
+   table_capacity = slots per replica of the OVERFLOW table (0 = default 64 N): every
+   bead first fills a private bucket of partners (128 slots = 1 KiB per bead; environment
+   GC_CONTACT_BUCKET overrides), only the excess spills. */
 int gc_set_contact_map(gc_ctx *ctx, double distance, int64_t interval,
                        int32_t scale_by_core, size_t table_capacity);
 /* contact_map::update on the current positions of every replica. */
