@@ -211,7 +211,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         int per_sm = 5;
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
-        ctx->tile_grid_x = std::max(4, (sms * per_sm + n_replicas - 1) / n_replicas);
+        ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
     }
     P.skin = 0.0f;
     P.kT = 1.0f;
@@ -786,8 +786,7 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
 // one force evaluation (+ update when fused) for every replica
 void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
 {
-    dim3 g(ctx->tile_grid_x, ctx->n_rep);
-    LAUNCH(ctx, k_pair_cells, g, CW * 32, ctx->hp, mask, use_enabled);
+    LAUNCH(ctx, k_pair_cells, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
     dim3 gf = bead_grid(ctx, BS);
     const int gr = ctx->n_rep;
     if (mode == STEP_FUSED) {
@@ -1308,7 +1307,9 @@ int gc_measure_fp32_peak(int32_t device, double *tflops)
     *tflops = 0.0;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return GC_ERR_CUDA;
-    return measure_fp32_peak(device, tflops) == cudaSuccess ? GC_OK : GC_ERR_CUDA;
+    // scalar FFMA chains, or (GC_PEAK_PACKED=1) packed fma.rn.f32x2 chains
+    const char *env = getenv("GC_PEAK_PACKED");
+    return measure_fp32_peak(device, tflops, env && atoi(env)) == cudaSuccess ? GC_OK : GC_ERR_CUDA;
 }
 
 int gc_profile_enable(gc_ctx *ctx, int32_t enabled)

@@ -27,7 +27,17 @@
 namespace gc {
 
 constexpr int CW = 4;                    // warps per block
-constexpr int CCAP = 480;                // candidates per tile chunk
+#ifndef GC_CCAP
+#define GC_CCAP 480
+#endif
+#ifndef GC_CELL_MINBLOCKS
+#define GC_CELL_MINBLOCKS 1
+#endif
+#ifndef GC_PACK_UNROLL
+#define GC_PACK_UNROLL 2
+#endif
+constexpr int kPackUnroll = GC_PACK_UNROLL;   // candidate pairs in flight per lane
+constexpr int CCAP = GC_CCAP;            // candidates per tile chunk
 constexpr int CHMAX = 16;                // home beads per pass
 constexpr int CGROUP = 2 * CHMAX;        // home beads per staged tile (two passes)
 
@@ -52,28 +62,63 @@ __device__ __forceinline__ void pair_accumulate(float xi, float yi, float zi, fl
     fz = fmaf(fac, ez, fz);
 }
 
+// The tile is stored as PAIRS of candidates per component so that the hot loop can
+// use Blackwell's packed FP32x2 instructions (fma.rn.f32x2 & co., SASS FFMA2 / FMUL2 /
+// FADD2): the FP32 pipe still retires 128 lanes per clock, but every issued
+// instruction now carries two pair evaluations, which takes the kernel off the
+// issue-slot limit (profiles/r1_notes.md).
 struct CellWarpSmem {
-    float4 tile[CCAP];                   // x, y, z, A'
-    float tileB[CCAP];                   // B'
+    float2 tx[CCAP / 2], ty[CCAP / 2], tz[CCAP / 2];
+    float2 tA[CCAP / 2], tB[CCAP / 2];   // pre-scaled mixing factors A', B'
     int row_off[33];                     // first flattened index of each row (+ sentinel)
     int row_shift[32];                   // slot = flattened index + row_shift[row]
 };
+static_assert(CCAP % 2 == 0, "candidates are staged in pairs");
 
-// Home-bead pass over the staged tile [0, nt): lanes = H beads x S slices,
-// slice s takes candidates s, s + S, s + 2 S, ...
+__device__ __forceinline__ float2 neg2(float2 v) { return make_float2(-v.x, -v.y); }
+__device__ __forceinline__ float2 max0(float2 v) { return make_float2(fmaxf(v.x, 0.0f), fmaxf(v.y, 0.0f)); }
+
+// Home-bead pass over the staged tile [0, nt): lanes = H beads x S slices; slice s
+// takes candidate pairs s, s + S, s + 2 S, ... (packed math), then the ragged tail
+// one candidate at a time.
 __device__ __forceinline__ void cell_pass(const CellWarpSmem &sm, int nt, int S, int s,
                                           float4 me, float Ai, float Bi, float kA2, float kB2,
                                           float &fx, float &fy, float &fz)
 {
-    const int full = nt / S;             // iterations in which every slice has a candidate
-    const float4 *tq = sm.tile + s;
-    const float *tb = sm.tileB + s;
-#pragma unroll 4
+    const int full = (nt >> 1) / S;      // iterations in which every slice has a whole pair
+    const float2 xi = make_float2(me.x, me.x), yi = make_float2(me.y, me.y), zi = make_float2(me.z, me.z);
+    const float2 Ai2 = make_float2(Ai, Ai), Bi2 = make_float2(Bi, Bi);
+    const float2 nkA = make_float2(-kA2, -kA2), kB = make_float2(kB2, kB2), one = make_float2(1.0f, 1.0f);
+    float2 ax = make_float2(0.f, 0.f), ay = ax, az = ax;
+#pragma unroll kPackUnroll
     for (int it = 0; it < full; it++) {
-        pair_accumulate(me.x, me.y, me.z, Ai, Bi, tq[it * S], tb[it * S], kA2, kB2, fx, fy, fz);
+        const int p = s + it * S;
+        const float2 ex = __fadd2_rn(xi, neg2(sm.tx[p]));
+        const float2 ey = __fadd2_rn(yi, neg2(sm.ty[p]));
+        const float2 ez = __fadd2_rn(zi, neg2(sm.tz[p]));
+        const float2 r2 = __ffma2_rn(ex, ex, __ffma2_rn(ey, ey, __fmul2_rn(ez, ez)));
+        const float2 gA = max0(__ffma2_rn(r2, nkA, one));
+        const float2 uB = __fmul2_rn(r2, kB);
+        const float2 uB2 = __fmul2_rn(uB, uB);
+        const float2 gB = max0(__ffma2_rn(neg2(uB2), uB2, one));
+        const float2 tA = __fmul2_rn(gA, gA);
+        const float2 tB = __fmul2_rn(__fmul2_rn(gB, gB), __fmul2_rn(uB2, uB));
+        const float2 fac = __ffma2_rn(__fadd2_rn(Bi2, sm.tB[p]), tB,
+                                      __fmul2_rn(__fadd2_rn(Ai2, sm.tA[p]), tA));
+        ax = __ffma2_rn(fac, ex, ax);
+        ay = __ffma2_rn(fac, ey, ay);
+        az = __ffma2_rn(fac, ez, az);
     }
-    if (s < nt - full * S) {             // ragged tail: the first nt % S slices
-        pair_accumulate(me.x, me.y, me.z, Ai, Bi, tq[full * S], tb[full * S], kA2, kB2, fx, fy, fz);
+    fx += ax.x + ax.y;
+    fy += ay.x + ay.y;
+    fz += az.x + az.y;
+    // ragged tail: candidates [2 full S, nt), fewer than 2 S + 1 of them
+    const float *sx = reinterpret_cast<const float *>(sm.tx), *sy = reinterpret_cast<const float *>(sm.ty);
+    const float *sz = reinterpret_cast<const float *>(sm.tz), *sA = reinterpret_cast<const float *>(sm.tA);
+    const float *sB = reinterpret_cast<const float *>(sm.tB);
+    for (int k = 2 * full * S + s; k < nt; k += S) {
+        pair_accumulate(me.x, me.y, me.z, Ai, Bi, make_float4(sx[k], sy[k], sz[k], sA[k]), sB[k], kA2,
+                        kB2, fx, fy, fz);
     }
 }
 
@@ -89,39 +134,46 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
     }
 }
 
-__global__ void __launch_bounds__(CW * 32) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
+__global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
     __shared__ CellWarpSmem s_warp[CW];
-    const int r = blockIdx.y;
-    RepState &st = P.st[r];
-    const StepConst &sc = st.sc;
-    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    const size_t ro = (size_t) r * P.n;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-    const float4 *__restrict__ sp = P.spos[st.parity] + ro;
-    const float2 *__restrict__ sab = P.sab + ro;
-    float4 *__restrict__ pforce = P.pforce + ro;
+    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
 
     if (!pair_on) {                                            // block-uniform
-        for (int t = blockIdx.x * (CW * 32) + threadIdx.x; t < P.n; t += gridDim.x * (CW * 32)) {
-            pforce[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const size_t total = (size_t) P.n_rep * P.n;
+        for (size_t t = (size_t) blockIdx.x * (CW * 32) + threadIdx.x; t < total;
+             t += (size_t) gridDim.x * (CW * 32)) {
+            P.pforce[t] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         return;
     }
 
+    const int M = P.cells_per_cut;
+    const int side = 2 * M + 1, nrows = side * side;
+    const bool plain = P.pair.mode == PAIR_PLAIN;
+    CellWarpSmem &sm = s_warp[warp];
+
+    // Blocks are not tied to a replica: every warp works through the queues of all
+    // replicas round-robin, starting at a different one, so an ensemble is balanced
+    // across the whole GPU whatever part of the grid is resident.
+    for (int rr = 0; rr < P.n_rep; rr++) {
+    const int r = (blockIdx.x + rr) % P.n_rep;
+    RepState &st = P.st[r];
+    const StepConst &sc = st.sc;
+    const size_t ro = (size_t) r * P.n;
+    const float4 *__restrict__ sp = P.spos[st.parity] + ro;
+    const float2 *__restrict__ sab = P.sab + ro;
+    float4 *__restrict__ pforce = P.pforce + ro;
     const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
     const int4 *__restrict__ cells = P.cell_list + ro;
     const int nused = st.n_used_cells;
     const int dx = st.dims[0], dxy = st.dims[0] * st.dims[1];
-    const int M = P.cells_per_cut;
-    const int side = 2 * M + 1, nrows = side * side;
-    const bool plain = P.pair.mode == PAIR_PLAIN;
     const float kA2 = sc.kA2, kB2 = sc.kB2;
     const float hA = 0.5f * sc.cA, hB = plain ? 0.0f : 0.5f * sc.cB;
-    CellWarpSmem &sm = s_warp[warp];
     // row `lane` of the (2M+1)^2 neighbour rows, relative to the home cell: the
     // grid has an M-cell halo (plan_grid), so every row exists
     const int row_rel = lane < nrows ? (lane % side - M) * dx + (lane / side - M) * dxy - M : 0;
@@ -196,8 +248,11 @@ __global__ void __launch_bounds__(CW * 32) k_pair_cells(const __grid_constant__ 
                             q.w = hA * ab.x;
                             qB = hB * ab.y;
                         }
-                        sm.tile[k - c0] = q;
-                        sm.tileB[k - c0] = qB;
+                        reinterpret_cast<float *>(sm.tx)[k - c0] = q.x;
+                        reinterpret_cast<float *>(sm.ty)[k - c0] = q.y;
+                        reinterpret_cast<float *>(sm.tz)[k - c0] = q.z;
+                        reinterpret_cast<float *>(sm.tA)[k - c0] = q.w;
+                        reinterpret_cast<float *>(sm.tB)[k - c0] = qB;
                     }
                 }
                 __syncwarp();
@@ -214,6 +269,7 @@ __global__ void __launch_bounds__(CW * 32) k_pair_cells(const __grid_constant__ 
             }
         }
     }
+    }   // replicas
 }
 
 } // namespace gc

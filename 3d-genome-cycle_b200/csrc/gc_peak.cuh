@@ -25,8 +25,25 @@ __global__ void __launch_bounds__(256) k_fp32_peak(float *out, float a, float b)
     if (s == 123.456f) out[0] = s;   // never true; keeps the chains alive
 }
 
-// Returns TFLOP/s (2 flop per FFMA), best of `reps`.
-inline cudaError_t measure_fp32_peak(int device, double *tflops)
+// The same with Blackwell's packed fma.rn.f32x2 (two FMAs per issued instruction).
+__global__ void __launch_bounds__(256) k_fp32x2_peak(float *out, float a, float b)
+{
+    float2 acc[PEAK_CHAINS / 2];
+#pragma unroll
+    for (int k = 0; k < PEAK_CHAINS / 2; k++) acc[k] = make_float2((float) (threadIdx.x + k), (float) k);
+    const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+    for (int it = 0; it < PEAK_ITERS; it++) {
+#pragma unroll
+        for (int k = 0; k < PEAK_CHAINS / 2; k++) acc[k] = __ffma2_rn(acc[k], a2, b2);
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < PEAK_CHAINS / 2; k++) s += acc[k].x + acc[k].y;
+    if (s == 123.456f) out[0] = s;
+}
+
+// Returns TFLOP/s (2 flop per FMA), best of `reps`; packed = 1 times the f32x2 variant.
+inline cudaError_t measure_fp32_peak(int device, double *tflops, int packed = 0)
 {
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return e;
@@ -41,7 +58,8 @@ inline cudaError_t measure_fp32_peak(int device, double *tflops)
     double best = 0.0;
     for (int rep = 0; rep < 6; rep++) {
         cudaEventRecord(t0);
-        k_fp32_peak<<<blocks, threads>>>(d, 0.999f, 0.001f);
+        if (packed) k_fp32x2_peak<<<blocks, threads>>>(d, 0.999f, 0.001f);
+        else k_fp32_peak<<<blocks, threads>>>(d, 0.999f, 0.001f);
         cudaEventRecord(t1);
         if ((e = cudaEventSynchronize(t1)) != cudaSuccess) break;
         float ms = 0.0f;
