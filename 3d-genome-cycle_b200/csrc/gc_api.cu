@@ -209,7 +209,10 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-        int per_sm = 5;
+        // resident blocks per SM of k_pair_cells (60 registers, 26 KB shared memory:
+        // __launch_bounds__(128, GC_CELL_MINBLOCKS)); measured best at 8, profiles/r1_notes.md
+        int per_sm = GC_CELL_MINBLOCKS;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells, CW * 32, 0);
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
     }

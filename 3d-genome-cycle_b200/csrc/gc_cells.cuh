@@ -7,15 +7,17 @@
 // list exists here.  Each WARP pops non-empty home cells from a per-replica work
 // queue (Params::cell_list, filled by k_gather) and, privately, with no block
 // barrier anywhere:
-//   1. lanes 0..8 fetch the slot ranges of the 9 contiguous x-rows of the 27
-//      neighbouring cells (the grid carries a one-cell halo, so there are no
-//      bounds checks); a warp scan flattens them into one candidate list;
+//   1. lanes 0..(2M+1)^2-1 fetch the slot ranges of the contiguous x-rows of the
+//      neighbouring cells (9 rows of 3 cells for M = 1; the grid carries an M-cell
+//      halo, so there are no bounds checks); a warp scan flattens them into one
+//      candidate list;
 //   2. the warp stages that list into ITS OWN shared-memory tile, coalesced per
 //      row, as (x, y, z, A') + B' with the A/B mixing factors pre-scaled;
 //   3. lanes split into H home beads x S candidate slices (H * S <= 32, chosen per
 //      cell) and evaluate EVERY staged candidate branch-free: the clamped soft
 //      cores vanish identically beyond their diameter, so there is no distance
-//      test, no ballot and no compaction (25 FP32 instructions per pair);
+//      test, no ballot and no compaction (packed FP32x2 math, 16.5 issued
+//      instructions per pair);
 //   4. S - 1 shuffles per component fold the slices and lanes < H store the force
 //      of their home bead (sorted-slot order, consumed by k_finish).
 // Every bead gathers its own force (full neighbourhood, no atomics), so the
@@ -28,10 +30,10 @@ namespace gc {
 
 constexpr int CW = 4;                    // warps per block
 #ifndef GC_CCAP
-#define GC_CCAP 480
+#define GC_CCAP 320
 #endif
 #ifndef GC_CELL_MINBLOCKS
-#define GC_CELL_MINBLOCKS 1
+#define GC_CELL_MINBLOCKS 8
 #endif
 #ifndef GC_PACK_UNROLL
 #define GC_PACK_UNROLL 2

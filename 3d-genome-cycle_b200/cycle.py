@@ -1,0 +1,113 @@
+"""One cell through the whole cycle on one GPU (BASELINE.json configs[1]), in the
+reference's stage order (scripts/simulate:44-47 plus the prometaphase / cycle programs):
+
+  anaphase -> telophase -> [spline refinement] -> relaxation -> interphase
+           -> [coarse-graining + sister copy] -> prometaphase -> [daughter cell]
+
+"Prophase condensation" and "G1 decondensation" have no dynamics of their own in the
+reference: condensation is the instantaneous coarse-graining, decondensation is the
+spline refinement followed by the core/bond-scale expansion schedule.
+Step counts default to the reference's (SIM/common/simulation_config.hpp:19-24,65-72);
+`scale_steps` shrinks them proportionally for tests.
+"""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+
+from . import stages, synth, transitions
+from .api import System
+
+
+def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_steps=1.0,
+                   log=None):
+    icfg = icfg or synth.InterphaseConfig()
+    mcfg = mcfg or synth.MitoticConfig()
+    design = design or synth.make_diploid_design(cfg=icfg)
+    md_ana = synth.make_mitotic_design(design, mcfg)
+    md_pro = synth.make_mitotic_design(design, mcfg, sisters=True)
+    nsteps = lambda k: max(int(round(k * scale_steps)), 1)   # noqa: E731
+    report = {"beads_interphase": design.n, "beads_anaphase": md_ana.n, "beads_prometaphase": md_pro.n,
+              "stages": []}
+
+    def timed(name, sys_, n_beads, steps, fn):
+        sys_.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        sys_.synchronize()
+        dt = time.perf_counter() - t0
+        e = sys_.compute_energy() / n_beads
+        row = {"stage": name, "beads": n_beads, "steps": steps, "seconds": dt,
+               "bead_steps_per_s": n_beads * steps / dt, "energy_per_bead": e}
+        report["stages"].append(row)
+        if log:
+            log(row)
+
+    # ---- anaphase / telophase (SIM/stage_anatelophase/simulation_driver.cpp:192-310) ----
+    ga = System(md_ana.n, 1, device)
+    ta = stages.setup_anatelophase(ga, md_ana, mcfg)
+    ga.set_seeds([seed])
+    ga.set_positions(synth.rod_positions(md_ana, mcfg, seed=seed))
+    stages.enter_anaphase(ga, ta)
+    n = nsteps(mcfg.anaphase_steps)
+    timed("anaphase", ga, md_ana.n, n, lambda: ga.run(n, mcfg.timestep))
+    stages.enter_telophase(ga, ta)
+    ga.set_seeds([seed + 1])
+    n = nsteps(mcfg.telophase_steps)
+    timed("telophase", ga, md_ana.n, n, lambda: ga.run(n, mcfg.timestep))
+    x_telo = ga.get_positions()
+    ga.close()
+
+    # ---- relaxation / interphase (SIM/stage_interphase/simulation_driver*.cpp) -----------
+    t0 = time.perf_counter()
+    x0 = synth.quantize_f32(transitions.transition_interphase(md_ana, design, x_telo)).astype(np.float64)
+    report["transition_interphase_s"] = time.perf_counter() - t0
+    gi = System(design.n, 1, device)
+    stages.setup_interphase(gi, design, icfg)
+    gi.set_seeds([seed + 2])
+    gi.set_positions(x0)
+    stages.begin_relaxation(gi, icfg)
+    n = nsteps(icfg.relaxation_steps)
+    timed("relaxation", gi, design.n, n,
+          lambda: gi.run(n, icfg.timestep, spacestep=icfg.relaxation_spacestep))
+    stages.begin_interphase(gi, icfg)
+    gi.set_seeds([seed + 3])
+    n = nsteps(icfg.steps)
+    window = icfg.sampling_interval * icfg.contactmap_output_window
+
+    def interphase():
+        done, first = 0, True
+        while done < n:
+            chunk = min(window, n - done)
+            gi.run(chunk, icfg.timestep, restart=first)
+            first = False
+            done += chunk
+            if done % window == 0:          # save_contacts + clear (simulation_driver_interphase.cpp:42-45)
+                report["contact_pairs_last_window"] = int(len(gi.contacts_fetch()))
+                gi.contacts_clear()
+    timed("interphase", gi, design.n, n, interphase)
+    ctx = gi.get_context()
+    report["interphase_end"] = {"time": ctx.time, "semiaxes": list(ctx.semiaxes),
+                                "core_scale": ctx.core_scale}
+    x_inter = gi.get_positions()
+    gi.close()
+
+    # ---- prometaphase (SIM/stage_prometaphase/simulation_driver.cpp:185-237) ---------------
+    t0 = time.perf_counter()
+    xp = synth.quantize_f32(transitions.transition_prometaphase(design, md_pro, mcfg, x_inter))
+    report["transition_prometaphase_s"] = time.perf_counter() - t0
+    gp = System(md_pro.n, 1, device)
+    stages.setup_prometaphase(gp, md_pro, mcfg)
+    gp.set_seeds([seed + 4])
+    gp.set_positions(xp.astype(np.float64))
+    n = nsteps(mcfg.prometaphase_steps)
+    timed("prometaphase", gp, md_pro.n, n, lambda: gp.run(n, mcfg.timestep))
+    x_meta = gp.get_positions()
+    gp.close()
+    report["next_anaphase_start"] = transitions.transition_cycle(md_pro, md_ana, mcfg, x_meta)
+    total_bs = sum(r["beads"] * r["steps"] for r in report["stages"])
+    total_s = sum(r["seconds"] for r in report["stages"])
+    report["total_seconds"] = total_s
+    report["bead_steps_per_s"] = total_bs / total_s
+    return report
