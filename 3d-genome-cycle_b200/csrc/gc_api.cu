@@ -68,6 +68,12 @@ struct gc_ctx {
     long long run_step = 0;     // host mirror of RepState::step
     int parity = 0;             // host mirror of RepState::parity (replicas move in lockstep)
     long long launches = 0;
+    // CUDA-graph replay of the fixed-timestep step loop (gc_run)
+    cudaGraphExec_t step_graph = nullptr;
+    int step_graph_steps = 0;       // steps per replay
+    long long step_graph_launches = 0;
+    Params step_graph_hp;           // kernel arguments baked into the graph
+    long long step_graph_interval = -1;
     double skin = 0.0;
     int tile_grid_x = 1;        // blocks per replica of the pair kernel
 
@@ -273,6 +279,7 @@ int gc_destroy(gc_ctx *ctx)
         for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
     }
     for (void *p : ctx->allocs) cudaFree(p);
+    if (ctx->step_graph) cudaGraphExecDestroy(ctx->step_graph);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return GC_OK;
@@ -801,6 +808,63 @@ void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
     }
 }
 
+void launch_contact_update(gc_ctx *ctx)
+{
+    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->hp, 0.0,
+           (int) RADIUS_CONTACT_PREV, -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+}
+
+void drop_step_graph(gc_ctx *ctx)
+{
+    if (ctx->step_graph) cudaGraphExecDestroy(ctx->step_graph);
+    ctx->step_graph = nullptr;
+    ctx->step_graph_steps = 0;
+}
+
+// The fixed-timestep loop launches the same 7 kernels with the same by-value Params
+// every step (all per-step state lives in RepState on the device), so a block of steps
+// is captured once and replayed: one graph launch instead of 7 B stream launches.  This
+// matters where the step is launch-bound (one replica, the ~600-bead mitotic stages).
+// With a contact cadence the block is one interval long and starts with the contact
+// update of the step just finished; otherwise it is 32 steps.
+bool ensure_step_graph(gc_ctx *ctx, long long interval)
+{
+    static const bool disabled = getenv("GC_NO_GRAPH") != nullptr;
+    if (disabled || ctx->profiling) return false;
+    if (interval > 64) return false;
+    if (ctx->step_graph && ctx->step_graph_interval == interval &&
+        memcmp(&ctx->step_graph_hp, &ctx->hp, sizeof(Params)) == 0) {
+        return true;
+    }
+    drop_step_graph(ctx);
+    const int B = interval > 0 ? (int) interval : 32;
+    const long long before = ctx->launches;
+    cudaGraph_t graph = nullptr;
+    if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    for (int k = 0; k < B; k++) {
+        launch_rebuild(ctx);
+        if (k == 0 && interval > 0) launch_contact_update(ctx);
+        launch_step(ctx, STEP_FUSED, 0u, 1);
+    }
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    ctx->step_graph_launches = ctx->launches - before;
+    ctx->launches = before;
+    if (e == cudaSuccess) e = cudaGraphInstantiate(&ctx->step_graph, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        ctx->step_graph = nullptr;
+        return false;
+    }
+    ctx->step_graph_steps = B;
+    ctx->step_graph_interval = interval;
+    memcpy(&ctx->step_graph_hp, &ctx->hp, sizeof(Params));
+    return true;
+}
+
 } // namespace
 
 extern "C" {
@@ -865,14 +929,25 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
 
     const long long interval = P.contact.enabled ? P.contact.interval : 0;
     const dim3 g = bead_grid(ctx, BS);
-    const dim3 gs = bead_grid(ctx, SBEADS);
-    for (long long i = 0; i < c->steps; i++) {
+    const bool graphable = !adaptive && !c->noise && c->steps >= 64 && ensure_step_graph(ctx, interval);
+    const int B = graphable ? ctx->step_graph_steps : 0;
+    for (long long i = 0; i < c->steps;) {
+        // a whole block, aligned to the contact cadence (the block opens with the contact
+        // update of the step just finished)
+        if (graphable && i > 0 && c->steps - i >= B &&
+            (interval == 0 || ctx->run_step % interval == 0)) {
+            GC_CUDA(ctx, cudaGraphLaunch(ctx->step_graph, ctx->stream));
+            ctx->launches += ctx->step_graph_launches;
+            ctx->run_step += B;
+            if (B & 1) ctx->parity ^= 1;
+            i += B;
+            continue;
+        }
         launch_rebuild(ctx);
         // contact update of the driver callback for the step just finished
         // (SIM/stage_interphase/simulation_driver_interphase.cpp:38-40)
         if (interval > 0 && ctx->run_step > 0 && ctx->run_step % interval == 0 && i > 0) {
-            LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
-                   (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+            launch_contact_update(ctx);
         }
         if (adaptive) {
             launch_step(ctx, STEP_FORCE, 0u, 1);
@@ -883,12 +958,12 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
         }
         ctx->run_step++;
         ctx->parity ^= 1;
+        i++;
     }
     // the callback of the last step of this chunk
     if (interval > 0 && c->steps > 0 && ctx->run_step % interval == 0) {
         launch_rebuild(ctx);
-        LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, gs, SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT_PREV, -1,
-               (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+        launch_contact_update(ctx);
     }
     return check_device_errors(ctx);
 }

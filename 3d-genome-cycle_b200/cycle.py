@@ -28,7 +28,8 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     md_ana = synth.make_mitotic_design(design, mcfg)
     md_pro = synth.make_mitotic_design(design, mcfg, sisters=True)
     nsteps = lambda k: max(int(round(k * scale_steps)), 1)   # noqa: E731
-    report = {"beads_interphase": design.n, "beads_anaphase": md_ana.n, "beads_prometaphase": md_pro.n,
+    report = {"beads_interphase": int(design.n), "beads_anaphase": int(md_ana.n),
+              "beads_prometaphase": int(md_pro.n),
               "stages": []}
 
     def timed(name, sys_, n_beads, steps, fn):
@@ -38,8 +39,9 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
         sys_.synchronize()
         dt = time.perf_counter() - t0
         e = sys_.compute_energy() / n_beads
-        row = {"stage": name, "beads": n_beads, "steps": steps, "seconds": dt,
-               "bead_steps_per_s": n_beads * steps / dt, "energy_per_bead": e}
+        n_beads = int(n_beads)
+        row = {"stage": name, "beads": n_beads, "steps": int(steps), "seconds": dt,
+               "bead_steps_per_s": n_beads * int(steps) / dt, "energy_per_bead": float(e)}
         report["stages"].append(row)
         if log:
             log(row)
@@ -106,7 +108,7 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     x_meta = gp.get_positions()
     gp.close()
     report["next_anaphase_start"] = transitions.transition_cycle(md_pro, md_ana, mcfg, x_meta)
-    total_bs = sum(r["beads"] * r["steps"] for r in report["stages"])
+    total_bs = sum(int(r["beads"]) * int(r["steps"]) for r in report["stages"])
     total_s = sum(r["seconds"] for r in report["stages"])
     report["total_seconds"] = total_s
     report["bead_steps_per_s"] = total_bs / total_s
