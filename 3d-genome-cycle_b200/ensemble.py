@@ -80,13 +80,19 @@ def reduce_sum(values, group=None):
 
 def keys_to_ijv(keys, counts) -> np.ndarray:
     """(i << 32 | j, count) -> the (i, j, count) triples contact_map::accumulate returns
-    (SIM/stage_interphase/contact_map.cpp:66-85)."""
-    k = keys.detach().cpu().numpy().astype(np.uint64)
-    out = np.empty((k.size, 3), dtype=np.uint32)
-    out[:, 0] = (k >> np.uint64(32)).astype(np.uint32)
-    out[:, 1] = (k & np.uint64(0xFFFFFFFF)).astype(np.uint32)
-    out[:, 2] = counts.detach().cpu().numpy().astype(np.uint32)
-    return out
+    (SIM/stage_interphase/contact_map.cpp:66-85).  CUDA tensors are unpacked on the device
+    and come back in one copy through pinned memory."""
+    import torch
+    k = keys.detach()
+    out = torch.empty((k.numel(), 3), dtype=torch.int32, device=k.device)
+    out[:, 0] = (k >> 32).to(torch.int32)
+    out[:, 1] = k.to(torch.int32)                      # low word (two's-complement wrap)
+    out[:, 2] = counts.detach().to(torch.int32)
+    if out.is_cuda:
+        host = torch.empty(out.shape, dtype=torch.int32, pin_memory=True)
+        host.copy_(out)
+        out = host
+    return out.numpy().view(np.uint32)
 
 
 def contact_probability(ijv: np.ndarray, chains: np.ndarray, n_updates: int, n_cells: int,

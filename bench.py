@@ -331,16 +331,28 @@ def run_b200_arm(args):
         # output window: ensemble contact map (device reduce per rank, NCCL gather, device
         # merge) and observables, inside the timed region
         t1 = time.perf_counter()
+        lap = {}
+
+        def mark(name, t_prev):
+            g.synchronize()
+            now = time.perf_counter()
+            lap[name] = (now - t_prev) * 1e3
+            return now
         keys, counts = g.contacts_reduce_device(-1, local)
+        tl = mark("device_reduce", t1)
         keys, counts = ens.gather_contacts(keys, counts,
                                            merge=lambda a, b: g.contacts_merge_device(a, b, local))
+        tl = mark("gather_merge", tl)
         rg2 = np.stack([g.radius_of_gyration2(design.chains, r) for r in range(R)])
         obs = torch.tensor(np.concatenate([rg2.sum(axis=0), [float(R)]]), dtype=torch.float64,
                            device=f"cuda:{local}")
         obs = ens.reduce_sum(obs).cpu().numpy()
+        tl = mark("rg2", tl)
         ijv = ens.keys_to_ijv(keys, counts) if rank == 0 else None
+        tl = mark("d2h_triples", tl)
         g.contacts_clear()
         barrier()
+        tl = mark("clear_barrier", tl)
         t_reduce = time.perf_counter() - t1
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local}")
@@ -357,7 +369,7 @@ def run_b200_arm(args):
             e2e["ensemble"] = {
                 "cells": world * R, "contact_pairs": int(len(ijv)),
                 "contact_counts": int(ijv[:, 2].sum()) if len(ijv) else 0,
-                "reduce_ms": t_reduce * 1e3,
+                "reduce_ms": t_reduce * 1e3, "reduce_breakdown_ms": {k: round(v, 3) for k, v in lap.items()},
                 "collective": "nccl all_gather of per-rank (key, count) runs + all_reduce of Rg^2"
                               if world > 1 else "none (1 rank)",
                 "rg_mean": float(np.sqrt(obs[:-1] / obs[-1]).mean()),
@@ -403,7 +415,11 @@ def run_b200_arm(args):
             "unit": "TFLOP/s", "frac": fp32_ach / fp32_peak if fp32_peak else None,
             "peak_source": "measured live: FFMA / FFMA2 chain microbenchmarks (gc_measure_fp32_peak), max of "
                            f"scalar {fp32_scalar:.2f} and packed {fp32_packed:.2f} TFLOP/s",
-            "traffic": None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one k_pair_cells launch from the
+            # committed ncu --set full capture of this workload (8 cells, relaxed state)
+            "traffic": 13.48e6 if (R == 8 and args.scale == 1.0 and name == "k_pair_cells") else None,
+            "traffic_source": "profiles/r1_pair_cells_v3_sparse_ncu_summary.txt (13.48 MB read, 0 B written "
+                              "per launch; algorithmic 32 B x R x N = %.2f MB)" % (32 * R * n / 1e6),
             "kernel_ms_per_launch": per_launch_s * 1e3, "kernel_launches_timed": cnt,
             "kernel_share_of_step": ms / total_ms if total_ms else None,
             "algorithmic_flop_per_bead_step": FLOP_PER_PAIR * useful + FLOP_SINGLE_BEAD,
