@@ -101,6 +101,11 @@ SYMBOLS = [
     ("gc_contacts_merge_device", C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_size_t,
                                            C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                            C.POINTER(C.c_size_t)]),
+    ("gc_decomp_configure", C.c_int, [_P, C.c_int32, C.c_int32]),
+    ("gc_decomp_buffers", C.c_int, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                    C.POINTER(C.c_size_t)]),
+    ("gc_decomp_step_compute", C.c_int, [_P]),
+    ("gc_decomp_step_commit", C.c_int, [_P]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
@@ -382,6 +387,29 @@ class System:
         self._ck(self.lib.gc_contacts_merge_device(self._h, keys.data_ptr(), counts.data_ptr(),
                                                    keys.numel(), C.byref(k), C.byref(v), C.byref(n)))
         return self._device_pairs(k, v, n, device)
+
+    # ---- spatial decomposition of one large replica (decomp.py drives it) -----
+    def decomp_configure(self, rank, world):
+        self._decomp_world = int(world)
+        self._ck(self.lib.gc_decomp_configure(self._h, int(rank), int(world)))
+
+    def decomp_buffers(self, device=0):
+        """(send, recv) as flat float32 CUDA tensors viewing the context's buffers:
+        send = [elems * 4], recv = [world * elems * 4]."""
+        import torch
+        a, b, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        self._ck(self.lib.gc_decomp_buffers(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        dev = torch.device("cuda", device)
+        send = torch.as_tensor(_DeviceArray(a.value, n.value * 4, "<f4"), device=dev)
+        world = self._decomp_world
+        recv = torch.as_tensor(_DeviceArray(b.value, world * n.value * 4, "<f4"), device=dev)
+        return send, recv
+
+    def decomp_step_compute(self):
+        self._ck(self.lib.gc_decomp_step_compute(self._h))
+
+    def decomp_step_commit(self):
+        self._ck(self.lib.gc_decomp_step_commit(self._h))
 
     # ---- observables / misc -----------------------------------------------
     def radius_of_gyration2(self, ranges, replica=0):

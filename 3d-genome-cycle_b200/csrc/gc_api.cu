@@ -20,6 +20,7 @@
 #include "gc_query.cuh"
 #include "gc_tile.cuh"
 #include "gc_cells.cuh"
+#include "gc_decomp.cuh"
 #include "gc_peak.cuh"
 
 using namespace gc;
@@ -883,6 +884,9 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
         return fail(ctx, GC_ERR_INVALID, "injected noise requires restart = 1");
     }
     Params &P = ctx->hp;
+    if (P.decomp && c->steps > 0) {
+        return fail(ctx, GC_ERR_STATE, "decomposed context: drive steps with gc_decomp_step_*");
+    }
     const bool adaptive = c->spacestep != 0.0;
     if (P.kT != (float) c->temperature || P.dt_cfg != c->timestep ||
         P.spacestep != (float) c->spacestep) {
@@ -1422,6 +1426,76 @@ int gc_launch_count(gc_ctx *ctx, int64_t *out)
 {
     if (!ctx || !out) return GC_ERR_INVALID;
     *out = ctx->launches;
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// spatial decomposition (gc_decomp.cuh)
+// ---------------------------------------------------------------------------
+int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world)
+{
+    GC_CHECK_CTX(ctx);
+    if (world < 1 || rank < 0 || rank >= world) return fail(ctx, GC_ERR_INVALID, "bad rank / world");
+    if (ctx->n_rep != 1) return fail(ctx, GC_ERR_STATE, "decomposition needs n_replicas = 1");
+    Params &P = ctx->hp;
+    if (P.dsend) dev_free(ctx, P.dsend);
+    if (P.drecv) dev_free(ctx, const_cast<float4 *>(P.drecv));
+    P.dsend = nullptr;
+    P.drecv = nullptr;
+    P.decomp = 0;
+    ctx->params_dirty = true;
+    if (world == 1) return GC_OK;
+    const int chunk = (ctx->n + world - 1) / world;
+    float4 *send = nullptr, *recv = nullptr;
+    int rc = dev_alloc(ctx, &send, (size_t) chunk + 2);
+    if (!rc) rc = dev_alloc(ctx, &recv, (size_t) world * ((size_t) chunk + 2));
+    if (rc) return rc;
+    GC_CUDA(ctx, cudaMemsetAsync(send, 0, ((size_t) chunk + 2) * sizeof(float4), ctx->stream));
+    P.decomp = 1;
+    P.dworld = world;
+    P.dchunk = chunk;
+    P.own_lo = std::min(rank * chunk, ctx->n);
+    P.own_hi = std::min(P.own_lo + chunk, ctx->n);
+    P.dsend = send;
+    P.drecv = recv;
+    return GC_OK;
+}
+
+int gc_decomp_buffers(gc_ctx *ctx, void **send, void **recv, size_t *elems)
+{
+    GC_CHECK_CTX(ctx);
+    if (!send || !recv || !elems) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    *send = ctx->hp.dsend;
+    *recv = const_cast<float4 *>(ctx->hp.drecv);
+    *elems = (size_t) ctx->hp.dchunk + 2;
+    return GC_OK;
+}
+
+int gc_decomp_step_compute(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    const Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    if (P.skin > 0.0f || P.spacestep != 0.0f || P.contact.enabled || P.noise) {
+        return fail(ctx, GC_ERR_STATE, "decomposed runs: fixed timestep, no skin, no contact map");
+    }
+    if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
+    launch_rebuild(ctx);
+    LAUNCH(ctx, k_pair_cells, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+    LAUNCH(ctx, k_finish<STEP_FUSED>, bead_grid(ctx, BS), BS, ctx->hp, 0u, 1);
+    LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);
+    return GC_OK;
+}
+
+int gc_decomp_step_commit(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    LAUNCH(ctx, k_decomp_scatter, (ctx->n + 255) / 256, 256, ctx->hp);
+    LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
+    ctx->run_step++;
+    ctx->parity ^= 1;
     return GC_OK;
 }
 

@@ -326,8 +326,11 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P
     if (rank == 0) {
         P.cell_count[(size_t) r * P.ncell_max + c] = 0;   // cursor back to 0
         // work queue of the pair kernel; its order is arbitrary but no result depends on it
-        int e = atomicAdd(&st.n_used_cells, 1);
-        P.cell_list[ro + e] = make_int4(c, base, end - base, 0);
+        // (a decomposed run only evaluates the cells that hold slots of this rank)
+        if (!P.decomp || (base < P.own_hi && end > P.own_lo)) {
+            int e = atomicAdd(&st.n_used_cells, 1);
+            P.cell_list[ro + e] = make_int4(c, base, end - base, 0);
+        }
     }
     int dst = base + rank;
     float4 p = P.pos[st.parity][ro + idx];

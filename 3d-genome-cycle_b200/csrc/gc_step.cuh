@@ -435,6 +435,7 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
     x.z = self4.z + fmaf(mudt, F.z, 0.5f * (W.z + Wp.z));
     x.w = 0.0f;
     P.pos[par ^ 1][ro + idx] = x;
+    if (P.decomp) P.dsend[t - P.own_lo] = make_float4(x.x, x.y, x.z, self4.w);   // halo exchange payload
     if (P.skin > 0.0f) {
         // cells may be reused: keep the sorted copy current and track the largest
         // displacement since the rebuild (neighbor_list.hpp:129-158)

@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P,
     StepRed red;
     red_init(red);
 
-    if (t < P.n) {
+    if (t < P.n && (!P.decomp || (t >= P.own_lo && t < P.own_hi))) {
         const size_t ro = (size_t) r * P.n;
         const float4 self4 = P.spos[st.parity][ro + t];
         const int idx = __float_as_int(self4.w);

@@ -189,6 +189,13 @@ struct Params {
     float4 *force;                 // total force, ORIGINAL order (adaptive stepper, gc_compute_force)
     float4 *pforce;                // nonbonded force, SORTED order (k_pair_cells -> k_finish)
     RepState *st;
+    // spatial decomposition of ONE large replica over several GPUs (gc_decomp.cuh):
+    // this rank evaluates and moves the sorted slots [own_lo, own_hi)
+    int decomp;                    // 0: off
+    int own_lo, own_hi;
+    int dworld, dchunk;            // ranks, slots per rank (= ceil(N / ranks))
+    float4 *dsend;                 // [dchunk + 2]: new (x, y, z, bead) of the owned slots + header
+    const float4 *drecv;           // [dworld][dchunk + 2]: every rank's dsend, gathered
     const float *noise;            // injected normals [R][steps][N][3] or null
     long long noise_steps;         // steps covered by `noise`
     long long noise_step0;         // st->step value that maps to noise row 0

@@ -254,6 +254,22 @@ int gc_contacts_reduce_device(gc_ctx *ctx, int32_t replica, uint64_t **keys, uin
 int gc_contacts_merge_device(gc_ctx *ctx, const uint64_t *keys_in, const uint32_t *counts_in,
                              size_t n_in, uint64_t **keys, uint32_t **counts, size_t *n);
 
+/* ---- spatial decomposition of one large replica over several GPUs --------
+   (BASELINE configs[4]; not in the reference, which is one process per cell.)
+   Every rank creates a context with n_replicas = 1 over ALL beads and calls
+   gc_decomp_configure(rank, world).  A step is then
+       gc_decomp_step_compute  -> all-gather of the send buffer into the receive
+       buffer (NCCL, on gc_stream)  -> gc_decomp_step_commit,
+   after gc_run(steps = 0, restart = 1) has set temperature / timestep.  The rank
+   evaluates and moves the sorted cell-list slots [rank C, (rank + 1) C), C =
+   ceil(n_beads / world); the trajectory is bit-identical for every world size.
+   Fixed timestep, no skin, no contact map.  world = 1 switches decomposition off. */
+int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world);
+/* Device buffers of float4: send = [elems], recv = [world][elems], elems = C + 2. */
+int gc_decomp_buffers(gc_ctx *ctx, void **send, void **recv, size_t *elems);
+int gc_decomp_step_compute(gc_ctx *ctx);
+int gc_decomp_step_commit(gc_ctx *ctx);
+
 /* ---- observables ------------------------------------------------------- */
 
 /* Squared radius of gyration per chain range [start, end) (harness-defined

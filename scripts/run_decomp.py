@@ -1,0 +1,110 @@
+"""BASELINE.json configs[4]: one synthetic polymer spread over the GPUs of a box by the
+slot-range decomposition of csrc/gc_decomp.cuh, one NCCL all-gather of the new positions
+per step (SURVEY.md 8d "Config 5": 1 chain x N beads at config-4 density, fixed dt,
+interphase force set).
+  torchrun --nproc-per-node G --master-addr 127.0.0.1 scripts/run_decomp.py --beads 2000000
+Prints one JSON line on rank 0: decomposed ms/step (CUDA events, max over ranks), the same
+polymer undecomposed on one GPU (rank 0), and with --check a bit-exact comparison of the
+two trajectories."""
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from gcpkg import gc_b200  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--beads", type=int, default=2_000_000)
+ap.add_argument("--steps", type=int, default=100)
+ap.add_argument("--warmup", type=int, default=20)
+ap.add_argument("--check", action="store_true")
+ap.add_argument("--out", default="")
+a = ap.parse_args()
+
+rank = int(os.environ.get("RANK", "0"))
+world = int(os.environ.get("WORLD_SIZE", "1"))
+local = int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+synth, stages, decomp = gc_b200.synth, gc_b200.stages, gc_b200.decomp
+semi = tuple(s * (a.beads / 1e5) ** (1 / 3) for s in (5.0, 4.0, 3.0))
+cfg = synth.InterphaseConfig(wall_semiaxes_init=semi, nucleolus_droplet_energy=0.0,
+                             wall_semiaxes_spring=(3e4 * a.beads / 60672,) * 3)
+design, x = synth.make_polymer(a.beads, seed=4, semiaxes=semi)
+
+
+def make():
+    g = gc_b200.System(design.n, 1, local)
+    stages.setup_interphase(g, design, cfg, contacts=False)
+    g.set_positions(x)
+    g.set_seeds([4])
+    stages.interphase_callback0(g, cfg)
+    return g
+
+
+def timed(fn, stream):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record(stream)
+    fn()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+rep = {"workload": f"1 chain x {design.n} beads, semiaxes {tuple(round(s, 2) for s in semi)}, interphase "
+                   "force set, fixed dt, wall ODE + expansion schedule on", "world": world,
+       "steps": a.steps, "warmup": a.warmup}
+x_dec = None
+if world > 1:
+    g = make()
+    run = decomp.DecomposedRun(g, rank, world, local)
+    run.begin(cfg.timestep)
+    run.step(a.warmup)
+    ms = timed(lambda: run.step(a.steps), run.stream)
+    g.synchronize()
+    rep["decomposed_ms_per_step"] = ms / a.steps
+    rep["decomposed_bead_steps_per_s"] = design.n * a.steps / (ms * 1e-3)
+    rep["exchange_bytes_per_rank_step"] = int(run.send.numel() * 4)
+    if a.check:
+        x_dec = g.get_positions(0)
+    g.close()
+if rank == 0:
+    g = make()
+    stream = torch.cuda.ExternalStream(g.stream(), device=local)
+    g.run(a.warmup, cfg.timestep, restart=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    g.run(a.steps, cfg.timestep, restart=False)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms1 = e0.elapsed_time(e1)
+    rep["single_gpu_ms_per_step"] = ms1 / a.steps
+    rep["single_gpu_bead_steps_per_s"] = design.n * a.steps / (ms1 * 1e-3)
+    if world > 1:
+        rep["speedup_vs_single_gpu"] = rep["single_gpu_ms_per_step"] / rep["decomposed_ms_per_step"]
+    if a.check and x_dec is not None:
+        rep["bit_identical_to_single_gpu"] = bool(np.array_equal(g.get_positions(0), x_dec))
+    g.close()
+    line = json.dumps(rep)
+    print(line)
+    if a.out:
+        Path(a.out).write_text(line + "\n")
+if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
