@@ -993,6 +993,7 @@ int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *o
 {
     GC_CHECK_CTX(ctx);
     if (!out || replica < 0 || replica >= ctx->n_rep) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "decomposed context: forces are partial per rank");
     int rc = finalize(ctx);
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
@@ -1483,7 +1484,8 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
     LAUNCH(ctx, k_pair_cells, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
-    LAUNCH(ctx, k_finish<STEP_FUSED>, bead_grid(ctx, BS), BS, ctx->hp, 0u, 1);
+    const int owned = P.own_hi - P.own_lo;
+    LAUNCH(ctx, k_finish<STEP_FUSED>, dim3(std::max((owned + BS - 1) / BS, 1), 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);
     return GC_OK;
 }
@@ -1492,7 +1494,7 @@ int gc_decomp_step_commit(gc_ctx *ctx)
 {
     GC_CHECK_CTX(ctx);
     if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
-    LAUNCH(ctx, k_decomp_scatter, (ctx->n + 255) / 256, 256, ctx->hp);
+    LAUNCH(ctx, k_decomp_scatter, std::min((ctx->n + 255) / 256, 148 * 8), 256, ctx->hp);
     LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
     ctx->run_step++;
     ctx->parity ^= 1;

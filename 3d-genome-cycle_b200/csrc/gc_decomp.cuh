@@ -36,34 +36,45 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
 __global__ void __launch_bounds__(256) k_decomp_scatter(const __grid_constant__ Params P)
 {
     RepState &st = P.st[0];
-    const int t = blockIdx.x * 256 + threadIdx.x;          // slot
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     bool bad = false;
-    if (t < P.n) {
+    float4 *__restrict__ out = P.pos[st.parity ^ 1];
+    for (int t = blockIdx.x * 256 + threadIdx.x; t < P.n; t += gridDim.x * 256) {      // slot
         const int k = t / P.dchunk;
         const float4 v = P.drecv[(size_t) k * (P.dchunk + 2) + (t - k * P.dchunk)];
-        const int idx = __float_as_int(v.w);
-        P.pos[st.parity ^ 1][idx] = make_float4(v.x, v.y, v.z, 0.0f);
-        lo[0] = hi[0] = v.x;
-        lo[1] = hi[1] = v.y;
-        lo[2] = hi[2] = v.z;
-        bad = !(fabsf(v.x) < INFINITY && fabsf(v.y) < INFINITY && fabsf(v.z) < INFINITY);
+        out[__float_as_int(v.w)] = make_float4(v.x, v.y, v.z, 0.0f);
+        lo[0] = fminf(lo[0], v.x); hi[0] = fmaxf(hi[0], v.x);
+        lo[1] = fminf(lo[1], v.y); hi[1] = fmaxf(hi[1], v.y);
+        lo[2] = fminf(lo[2], v.z); hi[2] = fmaxf(hi[2], v.z);
+        bad |= !(fabsf(v.x) < INFINITY && fabsf(v.y) < INFINITY && fabsf(v.z) < INFINITY);
     }
+    // block reduction, then 6 atomics per block
+    __shared__ float sh[8][6];
+    __shared__ int sh_bad;
+    if (threadIdx.x == 0) sh_bad = 0;
     for (int k = 0; k < 3; k++) {
         for (int o = 16; o > 0; o >>= 1) {
             lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
             hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
         }
     }
-    bad = __any_sync(0xffffffffu, bad);
-    if ((threadIdx.x & 31) == 0 && lo[0] <= hi[0]) {
-        for (int k = 0; k < 3; k++) {
-            atomicMin(&st.bbox_min[k], float_to_ordered(lo[k]));
-            atomicMax(&st.bbox_max[k], float_to_ordered(hi[k]));
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) {
+        for (int k = 0; k < 3; k++) { sh[wid][k] = lo[k]; sh[wid][3 + k] = hi[k]; }
+    }
+    if (bad) sh_bad = 1;
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float l = sh[0][threadIdx.x], h = sh[0][3 + threadIdx.x];
+        for (int w = 1; w < 8; w++) { l = fminf(l, sh[w][threadIdx.x]); h = fmaxf(h, sh[w][3 + threadIdx.x]); }
+        if (l <= h) {
+            atomicMin(&st.bbox_min[threadIdx.x], float_to_ordered(l));
+            atomicMax(&st.bbox_max[threadIdx.x], float_to_ordered(h));
         }
     }
-    if (bad && (threadIdx.x & 31) == 0) atomicExch(&st.error, 1);
-    if (t == 0) {
+    if (threadIdx.x == 0 && sh_bad) atomicExch(&st.error, 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         long long sum[4] = {0, 0, 0, 0};
         for (int k = 0; k < P.dworld; k++) {
             const long long *h = reinterpret_cast<const long long *>(P.drecv + (size_t) k * (P.dchunk + 2) + P.dchunk);

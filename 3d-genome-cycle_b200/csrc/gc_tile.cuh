@@ -19,11 +19,12 @@ __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P,
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    const int t = blockIdx.x * BS + threadIdx.x;
+    // a decomposed run launches only the blocks of the owned slot range
+    const int t = (P.decomp ? P.own_lo : 0) + blockIdx.x * BS + threadIdx.x;
     StepRed red;
     red_init(red);
 
-    if (t < P.n && (!P.decomp || (t >= P.own_lo && t < P.own_hi))) {
+    if (t < (P.decomp ? P.own_hi : P.n)) {
         const size_t ro = (size_t) r * P.n;
         const float4 self4 = P.spos[st.parity][ro + t];
         const int idx = __float_as_int(self4.w);

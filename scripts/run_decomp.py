@@ -25,6 +25,7 @@ ap.add_argument("--beads", type=int, default=2_000_000)
 ap.add_argument("--steps", type=int, default=100)
 ap.add_argument("--warmup", type=int, default=20)
 ap.add_argument("--check", action="store_true")
+ap.add_argument("--profile", type=int, default=0, help="per-kernel event timing over this many steps")
 ap.add_argument("--out", default="")
 a = ap.parse_args()
 
@@ -80,6 +81,14 @@ if world > 1:
     rep["decomposed_ms_per_step"] = ms / a.steps
     rep["decomposed_bead_steps_per_s"] = design.n * a.steps / (ms * 1e-3)
     rep["exchange_bytes_per_rank_step"] = int(run.send.numel() * 4)
+    if a.profile and rank == 0:
+        g.profile_enable(True)
+    if a.profile:
+        run.step(a.profile)
+        g.synchronize()
+    if a.profile and rank == 0:
+        rep["decomposed_kernels_ms"] = {k: round(v[1] / a.profile, 5) for k, v in g.profile_read().items()}
+        g.profile_enable(False)
     if a.check:
         x_dec = g.get_positions(0)
     g.close()
@@ -96,6 +105,11 @@ if rank == 0:
     ms1 = e0.elapsed_time(e1)
     rep["single_gpu_ms_per_step"] = ms1 / a.steps
     rep["single_gpu_bead_steps_per_s"] = design.n * a.steps / (ms1 * 1e-3)
+    if a.profile:
+        g.profile_enable(True)
+        g.run(a.profile, cfg.timestep, restart=False)
+        rep["single_gpu_kernels_ms"] = {k: round(v[1] / a.profile, 5) for k, v in g.profile_read().items()}
+        g.profile_enable(False)
     if world > 1:
         rep["speedup_vs_single_gpu"] = rep["single_gpu_ms_per_step"] / rep["decomposed_ms_per_step"]
     if a.check and x_dec is not None:
