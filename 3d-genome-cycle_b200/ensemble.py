@@ -78,6 +78,9 @@ def reduce_sum(values, group=None):
     return values
 
 
+_PINNED = None
+
+
 def keys_to_ijv(keys, counts) -> np.ndarray:
     """(i << 32 | j, count) -> the (i, j, count) triples contact_map::accumulate returns
     (SIM/stage_interphase/contact_map.cpp:66-85).  CUDA tensors are unpacked on the device
@@ -89,9 +92,12 @@ def keys_to_ijv(keys, counts) -> np.ndarray:
     out[:, 1] = k.to(torch.int32)                      # low word (two's-complement wrap)
     out[:, 2] = counts.detach().to(torch.int32)
     if out.is_cuda:
-        host = torch.empty(out.shape, dtype=torch.int32, pin_memory=True)
+        global _PINNED
+        if _PINNED is None or _PINNED.numel() < out.numel():     # page-locking is slow: keep it
+            _PINNED = torch.empty(int(out.numel() * 1.25) + 1024, dtype=torch.int32, pin_memory=True)
+        host = _PINNED[:out.numel()].view(out.shape)
         host.copy_(out)
-        out = host
+        return host.numpy().view(np.uint32)          # valid until the next call
     return out.numpy().view(np.uint32)
 
 
