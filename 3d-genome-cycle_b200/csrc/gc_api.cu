@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
@@ -69,6 +70,7 @@ struct gc_ctx {
     long long run_step = 0;     // host mirror of RepState::step
     int parity = 0;             // host mirror of RepState::parity (replicas move in lockstep)
     long long launches = 0;
+    bool pdl = true;                // programmatic dependent launch between the step's kernels
     // CUDA-graph replay of the fixed-timestep step loop (gc_run)
     cudaGraphExec_t step_graph = nullptr;
     int step_graph_steps = 0;       // steps per replay
@@ -222,6 +224,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells, CW * 32, 0);
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
+        ctx->pdl = getenv("GC_NO_PDL") == nullptr;
     }
     P.skin = 0.0f;
     P.kT = 1.0f;
@@ -655,10 +658,29 @@ void prof_clear(gc_ctx *ctx)
     ctx->prof_events = 0;
 }
 
+// Every launch carries the programmatic-stream-serialization attribute (unless
+// GC_NO_PDL is set): the kernels open with GC_PDL_ENTRY, so kernel N + 1 is scheduled
+// while kernel N drains and the kernel-to-kernel gap (7 boundaries per step) shrinks.
+template<typename... KArgs, typename... Args>
+inline void launch_k(gc_ctx *ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 #define LAUNCH(ctx, kernel, grid, block, ...)                                                 \
     do {                                                                                      \
         prof_begin(ctx, #kernel);                                                             \
-        kernel<<<grid, block, 0, (ctx)->stream>>>(__VA_ARGS__);                               \
+        launch_k(ctx, kernel, dim3(grid), dim3(block), __VA_ARGS__);                          \
         prof_end(ctx);                                                                        \
         (ctx)->launches++;                                                                    \
     } while (0)
@@ -786,6 +808,7 @@ int check_device_errors(gc_ctx *ctx)
 
 __global__ void k_restart(const __grid_constant__ Params P, double dt)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];

@@ -139,6 +139,7 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
 __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
+    GC_PDL_ENTRY();
     __shared__ CellWarpSmem s_warp[CW];
 
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);

@@ -22,6 +22,7 @@ namespace gc {
 // after k_finish: this rank's partial wall statistics -> header of the send buffer
 __global__ void k_decomp_header(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     RepState &st = P.st[0];
     long long *h = reinterpret_cast<long long *>(P.dsend + P.dchunk);
@@ -35,6 +36,7 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
 // beads (the next grid plan), wall statistics summed over ranks in rank order
 __global__ void __launch_bounds__(256) k_decomp_scatter(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     RepState &st = P.st[0];
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     bool bad = false;

@@ -125,6 +125,7 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
 
 __global__ void k_reset_reductions(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];
@@ -141,6 +142,7 @@ __global__ void k_reset_reductions(const __grid_constant__ Params P)
 
 __global__ void k_bbox(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.y;
     RepState &st = P.st[r];
     const float4 *pos = P.pos[st.parity] + (size_t) r * P.n;
@@ -179,6 +181,7 @@ __global__ void k_bbox(const __grid_constant__ Params P)
 
 __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.y;
     const RepState &st = P.st[r];
     if (!st.need_rebuild) return;
@@ -205,6 +208,7 @@ constexpr unsigned long long SCAN_VALUE = (1ull << 62) - 1;
 
 __global__ void __launch_bounds__(SCAN_BS) k_scan(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;
@@ -297,6 +301,7 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan(const __grid_constant__ Params
 
 __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.y;
     const RepState &st = P.st[r];
     if (!st.need_rebuild) return;
@@ -310,6 +315,7 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
 
 __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.y;
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;

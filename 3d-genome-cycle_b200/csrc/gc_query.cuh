@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(SBS) k_pairs(const __grid_constant__ Params P,
                                                unsigned long long out_cap,
                                                unsigned long long *out_count)
 {
+    GC_PDL_ENTRY();
     __shared__ PairWalkSmem s_walk[SWARPS];
     const int r = blockIdx.y;
     RepState &st = P.st[r];
@@ -136,6 +137,7 @@ __global__ void k_contact_compact(const __grid_constant__ Params P, int replica,
                                   unsigned long long *out_keys, unsigned int *out_vals,
                                   unsigned long long *out_count)
 {
+    GC_PDL_ENTRY();
     const ContactParams &C = P.contact;
     const unsigned long long nrep = replica < 0 ? (unsigned long long) P.n_rep : 1ull;
     const unsigned long long r0 = replica < 0 ? 0ull : (unsigned long long) replica;
@@ -167,6 +169,7 @@ __global__ void k_contact_compact(const __grid_constant__ Params P, int replica,
 __global__ void __launch_bounds__(BS) k_energy(const __grid_constant__ Params P, int r, unsigned mask_arg,
                                                double *partials)
 {
+    GC_PDL_ENTRY();
     RepState &st = P.st[r];
     const StepConst &sc = st.sc;
     const unsigned mask = mask_arg & P.enabled;
@@ -297,6 +300,7 @@ __global__ void __launch_bounds__(BS) k_energy(const __grid_constant__ Params P,
 
 __global__ void k_debug_noise(const __grid_constant__ Params P, int r, long long step, float *out)
 {
+    GC_PDL_ENTRY();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
     f3 z = normal3(P.st[r].seed, (uint32_t) i, step);
@@ -308,6 +312,7 @@ __global__ void k_debug_noise(const __grid_constant__ Params P, int r, long long
 // Squared radius of gyration of bead ranges [start, end): one block per range.
 __global__ void k_rg2(const __grid_constant__ Params P, int r, int n_ranges, const int *ranges, double *out)
 {
+    GC_PDL_ENTRY();
     int g = blockIdx.x;
     if (g >= n_ranges) return;
     const float4 *pos = P.pos[P.st[r].parity] + (size_t) r * P.n;

@@ -467,6 +467,7 @@ __device__ __forceinline__ float solve_timestep(float spacestep, float mu, float
 // Second half of an adaptive step: update with the globally reduced dt.
 __global__ void __launch_bounds__(BS) k_integrate(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const int t = blockIdx.x * BS + threadIdx.x;
@@ -511,6 +512,7 @@ static_assert(sizeof(RepState) % sizeof(int) == 0, "RepState is copied word by w
 // after k_finish<STEP_FUSED> (fixed dt) or k_integrate (adaptive dt)
 __global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Params P, int adaptive)
 {
+    GC_PDL_ENTRY();
     __shared__ RepState s;
     const int r = blockIdx.x, lane = threadIdx.x;
     repstate_load(s, P.st[r], lane);
@@ -531,6 +533,7 @@ __global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Pa
 // (MD/simulation/detail/brownian_timestepper.hpp:109-136: global minimum)
 __global__ void __launch_bounds__(32) k_finalize_force(const __grid_constant__ Params P)
 {
+    GC_PDL_ENTRY();
     __shared__ RepState s;
     const int r = blockIdx.x, lane = threadIdx.x;
     repstate_load(s, P.st[r], lane);
@@ -548,6 +551,7 @@ __global__ void __launch_bounds__(32) k_finalize_force(const __grid_constant__ P
 // radius_override > 0 forces the list radius (gc_neighbor_pairs).
 __global__ void k_plan(const __grid_constant__ Params P, double radius_override)
 {
+    GC_PDL_ENTRY();
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_rep) return;
     RepState &st = P.st[r];

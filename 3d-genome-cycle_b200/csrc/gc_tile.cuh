@@ -16,6 +16,7 @@ namespace gc {
 template<int MODE>
 __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P, unsigned mask_arg, int use_enabled)
 {
+    GC_PDL_ENTRY();
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);

@@ -26,6 +26,20 @@
 // fixed-point scale of the wall-reaction accumulators (deterministic sums)
 #define GC_FX_SCALE 4294967296.0 /* 2^32 */
 
+// Programmatic dependent launch: every kernel waits for its predecessor to complete and
+// flush (a no-op for launches without the attribute), which lets the driver stage the
+// launch while the predecessor still runs.  Triggering the successor EARLY
+// (griddepcontrol.launch_dependents at entry, GC_PDL_TRIGGER = 1) was measured slower:
+// its blocks take SM slots from the draining grid (profiles/r1_notes.md).
+#ifndef GC_PDL_TRIGGER
+#define GC_PDL_TRIGGER 0
+#endif
+#define GC_PDL_ENTRY()                                                                \
+    do {                                                                              \
+        if (GC_PDL_TRIGGER) asm volatile("griddepcontrol.launch_dependents;");        \
+        asm volatile("griddepcontrol.wait;" ::: "memory");                            \
+    } while (0)
+
 namespace gc {
 
 enum PairMode : int { PAIR_NONE = 0, PAIR_AB = 1, PAIR_PLAIN = 2 };

@@ -400,6 +400,19 @@ def run_b200_arm(args):
         cnow = g.get_context(0)
         dcut = max(cfg.a_core_diameter, cfg.b_core_diameter) * cnow.core_scale
         useful = len(g.neighbor_pairs(dcut, replica=0)) / n      # unordered pairs within dcut per bead
+        # pair evaluations the kernel actually EXECUTES: every home bead against every bead of
+        # its 27 cells of edge dcut (gather over cubic cells, full neighbourhood)
+        xs = g.get_positions(0)
+        ci = np.floor((xs - xs.min(axis=0)) / dcut).astype(np.int64) + 1
+        dims = ci.max(axis=0) + 2
+        occ = np.zeros(tuple(dims), dtype=np.int64)
+        np.add.at(occ, (ci[:, 0], ci[:, 1], ci[:, 2]), 1)
+        cand = np.zeros_like(occ)
+        for dx in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                for dz in (-1, 0, 1):
+                    cand += np.roll(occ, (dx, dy, dz), axis=(0, 1, 2))
+        executed_pairs = float((occ * cand).sum()) * R
         peaks = {}
         pk = ROOT / "MEASURED_PEAKS.json"
         if pk.exists():
@@ -427,6 +440,12 @@ def run_b200_arm(args):
             "traffic": 13.48e6 if (R == 8 and args.scale == 1.0 and name == "k_pair_cells") else None,
             "traffic_source": "profiles/r1_pair_cells_v3_sparse_ncu_summary.txt (13.48 MB read, 0 B written "
                               "per launch; algorithmic 32 B x R x N = %.2f MB)" % (32 * R * n / 1e6),
+            "executed": {"pair_evaluations_per_launch": executed_pairs, "flop_per_pair_evaluation": FLOP_PER_PAIR,
+                         "achieved": executed_pairs * FLOP_PER_PAIR / per_launch_s / 1e12, "unit": "TFLOP/s",
+                         "frac": executed_pairs * FLOP_PER_PAIR / per_launch_s / 1e12 / fp32_peak if fp32_peak else None,
+                         "note": "work the branch-free gather executes (27 cells of edge dcut, both directions "
+                                 "of every pair) = %.1fx the algorithmic pair count" % (
+                                     executed_pairs / max(useful * beads_per_launch, 1.0))},
             "kernel_ms_per_launch": per_launch_s * 1e3, "kernel_launches_timed": cnt,
             "kernel_share_of_step": ms / total_ms if total_ms else None,
             "algorithmic_flop_per_bead_step": FLOP_PER_PAIR * useful + FLOP_SINGLE_BEAD,
