@@ -273,49 +273,64 @@ __device__ __forceinline__ void block_reduce_commit(RepState &st, StepRed &s, bo
                                                     bool with_geom, bool with_dt)
 {
     constexpr int NW = NT / 32;
-    __shared__ float sh_f[NW][8];
+    __shared__ int sh_i[NW][8];
     __shared__ long long sh_l[NW][4];
-    __shared__ int sh_bad;
+    __shared__ int sh_bad, sh_wall;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) sh_bad = 0;
+    if (threadIdx.x == 0) { sh_bad = 0; sh_wall = 0; }
 
-    float v[8];
-    for (int k = 0; k < 3; k++) { v[k] = warp_min(s.lo[k]); v[3 + k] = warp_max(s.hi[k]); }
-    v[6] = warp_max(s.disp2);
-    v[7] = warp_min(s.dtmin);
-    long long q[4];
-    q[0] = warp_sum(__double2ll_rn((double) s.w.ax * GC_FX_SCALE));
-    q[1] = warp_sum(__double2ll_rn((double) s.w.ay * GC_FX_SCALE));
-    q[2] = warp_sum(__double2ll_rn((double) s.w.az * GC_FX_SCALE));
-    q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
+    // warp level: one REDUX per value on order-preserving integer images of the floats
+    // (disp2 >= 0 and dt > 0 are ordered as unsigned bit patterns already)
+    int v[8] = {0, 0, 0, 0, 0, 0, 0, 0x7f800000};
+    if (with_geom) {
+        for (int k = 0; k < 3; k++) {
+            v[k] = __reduce_min_sync(0xffffffffu, float_to_ordered(s.lo[k]));
+            v[3 + k] = __reduce_max_sync(0xffffffffu, float_to_ordered(s.hi[k]));
+        }
+        v[6] = (int) __reduce_max_sync(0xffffffffu, __float_as_uint(s.disp2 != s.disp2 ? NAN : s.disp2));
+    }
+    if (with_dt) v[7] = (int) __reduce_min_sync(0xffffffffu, __float_as_uint(s.dtmin));
+    // the wall touches few beads: warps without a contribution skip the 64-bit sums
+    long long q[4] = {0, 0, 0, 0};
+    const bool wall_any = with_wall && __any_sync(0xffffffffu, s.w.ax != 0.0f || s.w.ay != 0.0f ||
+                                                                  s.w.az != 0.0f || s.w.reaction != 0.0f);
+    if (wall_any) {
+        q[0] = warp_sum(__double2ll_rn((double) s.w.ax * GC_FX_SCALE));
+        q[1] = warp_sum(__double2ll_rn((double) s.w.ay * GC_FX_SCALE));
+        q[2] = warp_sum(__double2ll_rn((double) s.w.az * GC_FX_SCALE));
+        q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
+    }
     bool bad = __any_sync(0xffffffffu, s.bad);
     __syncthreads();
     if (lane == 0) {
-        for (int k = 0; k < 8; k++) sh_f[wid][k] = v[k];
+        for (int k = 0; k < 8; k++) sh_i[wid][k] = v[k];
         for (int k = 0; k < 4; k++) sh_l[wid][k] = q[k];
         if (bad) sh_bad = 1;
+        if (wall_any) sh_wall = 1;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < NW; w++) {
             for (int k = 0; k < 3; k++) {
-                v[k] = fminf(v[k], sh_f[w][k]);
-                v[3 + k] = fmaxf(v[3 + k], sh_f[w][3 + k]);
+                v[k] = min(v[k], sh_i[w][k]);
+                v[3 + k] = max(v[3 + k], sh_i[w][3 + k]);
             }
-            v[6] = fmaxf(v[6], sh_f[w][6]);
-            v[7] = fminf(v[7], sh_f[w][7]);
+            v[6] = (int) max((unsigned) v[6], (unsigned) sh_i[w][6]);
+            v[7] = (int) min((unsigned) v[7], (unsigned) sh_i[w][7]);
             for (int k = 0; k < 4; k++) q[k] += sh_l[w][k];
         }
         if (with_geom) {
             for (int k = 0; k < 3; k++) {
-                atomicMin(&st.bbox_min[k], float_to_ordered(v[k]));
-                atomicMax(&st.bbox_max[k], float_to_ordered(v[3 + k]));
+                if (v[k] <= v[3 + k]) {                     // a block of idle threads holds +-inf
+                    atomicMin(&st.bbox_min[k], v[k]);
+                    atomicMax(&st.bbox_max[k], v[3 + k]);
+                }
             }
             // NaN displacement: bits compare above every finite value
-            atomicMax(&st.maxdisp2_bits, __float_as_uint(v[6] != v[6] ? NAN : v[6]));
+            atomicMax(&st.maxdisp2_bits, (unsigned) v[6]);
         }
-        if (with_dt) atomicMin(&st.dtmin_bits, __float_as_uint(v[7]));
-        if (with_wall) {
+        if (with_dt) atomicMin(&st.dtmin_bits, (unsigned) v[7]);
+        if (with_wall && sh_wall) {
             for (int k = 0; k < 3; k++) {
                 if (q[k]) atomicAdd((unsigned long long *) &st.axial_fx[k], (unsigned long long) q[k]);
             }
