@@ -510,9 +510,17 @@ __global__ void __launch_bounds__(BS) k_integrate(const __grid_constant__ Params
 // dependent global round trips.
 __device__ __forceinline__ void repstate_load(RepState &dst, const RepState &src, int lane)
 {
+    // all loads first (one round trip), then the stores
+    constexpr int W = (int) (sizeof(RepState) / sizeof(int)), J = (W + 31) / 32;
     const int *s = reinterpret_cast<const int *>(&src);
     int *d = reinterpret_cast<int *>(&dst);
-    for (int k = lane; k < (int) (sizeof(RepState) / sizeof(int)); k += 32) d[k] = s[k];
+    int tmp[J];
+#pragma unroll
+    for (int j = 0; j < J; j++) tmp[j] = lane + 32 * j < W ? s[lane + 32 * j] : 0;
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+        if (lane + 32 * j < W) d[lane + 32 * j] = tmp[j];
+    }
     __syncwarp();
 }
 __device__ __forceinline__ void repstate_store(RepState &dst, const RepState &src, int lane)
