@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
     float4 *__restrict__ pforce = P.pforce + ro;
     const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
     const int4 *__restrict__ cells = P.cell_list + ro;
-    const int nused = st.n_used_cells;
+    const int nheavy = st.n_used_cells, nused = nheavy + st.n_light_cells;
     const int dx = st.dims[0], dxy = st.dims[0] * st.dims[1];
     const float kA2 = sc.kA2, kB2 = sc.kB2;
     const float hA = 0.5f * sc.cA, hB = plain ? 0.0f : 0.5f * sc.cB;
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
         if (lane == 0) kk = atomicAdd(&st.cell_cursor, 1);
         kk = __shfl_sync(0xffffffffu, kk, 0);
         if (kk >= nused) break;
-        const int4 cell = __ldg(&cells[kk]);
+        const int4 cell = __ldg(&cells[kk < nheavy ? kk : P.n - 1 - (kk - nheavy)]);
         const int c = cell.x, h0 = cell.y, nhome = cell.z;
 
         // ---- 1. candidate rows -> flattened list -------------------------------

@@ -17,6 +17,9 @@ namespace gc {
 
 constexpr int BS = 128;          // threads per block of the per-bead kernels
 constexpr int SCAN_BS = 1024;
+#ifndef GC_HEAVY_CELL
+#define GC_HEAVY_CELL 12
+#endif
 
 // ---------------------------------------------------------------------------
 // small helpers
@@ -188,7 +191,7 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     // reset the scan's look-back words, its ticket and the used-cell list
     if (i < P.scan_blocks) P.scan_status[(size_t) r * P.scan_blocks + i] = 0ull;
-    if (i == 0) { P.st[r].scan_ticket = 0; P.st[r].n_used_cells = 0; }
+    if (i == 0) { P.st[r].scan_ticket = 0; P.st[r].n_used_cells = 0; P.st[r].n_light_cells = 0; }
     if (i >= P.n) return;
     float4 p = P.pos[st.parity][(size_t) r * P.n + i];
     int c = cell_index(st, p, P.cells_per_cut);
@@ -334,8 +337,15 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P
         // work queue of the pair kernel; its order is arbitrary but no result depends on it
         // (a decomposed run only evaluates the cells that hold slots of this rank)
         if (!P.decomp || (base < P.own_hi && end > P.own_lo)) {
-            int e = atomicAdd(&st.n_used_cells, 1);
-            P.cell_list[ro + e] = make_int4(c, base, end - base, 0);
+            // well populated cells are queued from the front, the rest from the back:
+            // the pair kernel then starts on the heavy ones and fills its tail with
+            // light ones (longest-processing-time-first)
+            const int4 item = make_int4(c, base, end - base, 0);
+            if (end - base >= GC_HEAVY_CELL) {
+                P.cell_list[ro + atomicAdd(&st.n_used_cells, 1)] = item;
+            } else {
+                P.cell_list[ro + P.n - 1 - atomicAdd(&st.n_light_cells, 1)] = item;
+            }
         }
     }
     int dst = base + rank;

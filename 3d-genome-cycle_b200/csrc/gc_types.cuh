@@ -153,7 +153,7 @@ struct RepState {
     unsigned int dtmin_bits;       // adaptive dt candidate (float bits)
     int bbox_min[3], bbox_max[3];  // order-preserving int encoding of floats
     int scan_ticket;               // block order of the chained cell scan
-    int n_used_cells;              // entries of Params::cell_list (non-empty cells)
+    int n_used_cells;              // heavy entries of Params::cell_list (from the front)
     int cell_cursor;               // work-queue head of the pair kernel, reset every step
     // --- cell grid ---
     int need_rebuild;
@@ -164,7 +164,7 @@ struct RepState {
     float cell_size, inv_cell;
     float rc_valid;                // interaction radius the current cells guarantee
     int error;                     // sticky: 1 = NaN/Inf seen
-    int pad;
+    int n_light_cells;             // lightly populated cells, queued from the BACK of cell_list
     StepConst sc;
 };
 
