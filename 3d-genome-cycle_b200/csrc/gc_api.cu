@@ -21,6 +21,7 @@
 #include "gc_query.cuh"
 #include "gc_tile.cuh"
 #include "gc_cells.cuh"
+#include "gc_contact.cuh"
 #include "gc_decomp.cuh"
 #include "gc_peak.cuh"
 
@@ -834,8 +835,7 @@ void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
 
 void launch_contact_update(gc_ctx *ctx)
 {
-    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->hp, 0.0,
-           (int) RADIUS_CONTACT_PREV, -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+    LAUNCH(ctx, k_contact_cells, ctx->tile_grid_x, CW * 32, ctx->hp, (int) RADIUS_CONTACT_PREV);
 }
 
 void drop_step_graph(gc_ctx *ctx)
@@ -1152,8 +1152,7 @@ int gc_contacts_update(gc_ctx *ctx)
     if (rc) return rc;
     plan_and_rebuild(ctx, 0.0);
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_pairs<PAIRS_CONTACT>, bead_grid(ctx, SBEADS), SBS, ctx->hp, 0.0, (int) RADIUS_CONTACT,
-           -1, (uint2 *) nullptr, 0ull, (unsigned long long *) nullptr);
+    LAUNCH(ctx, k_contact_cells, ctx->tile_grid_x, CW * 32, ctx->hp, (int) RADIUS_CONTACT);
     return check_device_errors(ctx);
 }
 

@@ -141,6 +141,7 @@ __global__ void k_reset_reductions(const __grid_constant__ Params P)
     st.maxdisp2_bits = 0u;
     st.dtmin_bits = 0x7f800000u;
     st.cell_cursor = 0;
+    st.contact_cursor = 0;
 }
 
 __global__ void k_bbox(const __grid_constant__ Params P)

@@ -406,6 +406,7 @@ __device__ inline void finalize_step(const Params &P, RepState &st, double dt_us
     }
     st.dtmin_bits = 0x7f800000u;
     st.cell_cursor = 0;
+    st.contact_cursor = 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -567,6 +568,7 @@ __global__ void __launch_bounds__(32) k_finalize_force(const __grid_constant__ P
         s.sc.dt_cur = dtc;
         s.dtmin_bits = 0x7f800000u;
         s.cell_cursor = 0;
+        s.contact_cursor = 0;
     }
     repstate_store(P.st[r], s, lane);
 }
@@ -585,6 +587,7 @@ __global__ void k_plan(const __grid_constant__ Params P, double radius_override)
     st.maxdisp2_bits = 0u;
     st.rebuilds += 1;
     st.cell_cursor = 0;
+    st.contact_cursor = 0;
     // the next step accumulates its own bounding box from scratch
     for (int k = 0; k < 3; k++) {
         st.bbox_min[k] = 0x7fffffff;

@@ -165,6 +165,8 @@ struct RepState {
     float rc_valid;                // interaction radius the current cells guarantee
     int error;                     // sticky: 1 = NaN/Inf seen
     int n_light_cells;             // lightly populated cells, queued from the BACK of cell_list
+    int contact_cursor;            // work-queue head of k_contact_cells
+    int pad2;
     StepConst sc;
 };
 
