@@ -71,6 +71,7 @@ SYMBOLS = [
     ("gc_get_positions", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_set_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
     ("gc_get_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
+    ("gc_get_frame", C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     ("gc_set_seeds", C.c_int, [_P, C.POINTER(C.c_uint64)]),
     ("gc_add_pair_softcore_ab", C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32]),
     ("gc_add_pair_softcore", C.c_int, [_P, C.c_double, C.c_double]),
@@ -228,6 +229,13 @@ class System:
         x = np.empty((self.n, 3), dtype=np.float32)
         self._ck(self.lib.gc_get_positions_f32(self._h, replica, _ptr(x, C.c_float)))
         return x
+
+    def get_frame(self, replica=0, fraction_bits=16):
+        """Quantised f32 frame as the reference stores it; replica = -1: [R, n, 3]."""
+        nrep = self.n_rep if replica < 0 else 1
+        out = np.empty((nrep, self.n, 3), dtype=np.float32)
+        self._ck(self.lib.gc_get_frame(self._h, int(replica), int(fraction_bits), _ptr(out, C.c_float)))
+        return out if replica < 0 else out[0]
 
     def set_seeds(self, seeds):
         s = np.ascontiguousarray(seeds, dtype=np.uint64)

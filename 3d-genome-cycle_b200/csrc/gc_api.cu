@@ -61,6 +61,8 @@ struct gc_ctx {
     TripleEntry *d_triple_ent = nullptr;
     TetherEntry *d_tether_ent = nullptr;
     int *d_well_targets = nullptr;
+    float *d_frame = nullptr;   // gc_get_frame staging
+    size_t frame_cap = 0;
     float *d_noise = nullptr;
     size_t noise_cap = 0;
     double *d_partials = nullptr;
@@ -993,6 +995,31 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
         launch_contact_update(ctx);
     }
     return check_device_errors(ctx);
+}
+
+int gc_get_frame(gc_ctx *ctx, int32_t replica, int32_t fraction_bits, float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz || replica < -1 || replica >= ctx->n_rep || fraction_bits < 1 || fraction_bits > 24) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    const int r0 = replica < 0 ? 0 : replica, nrep = replica < 0 ? ctx->n_rep : 1;
+    const size_t count = (size_t) nrep * ctx->n * 3;
+    if (count == 0) return GC_OK;
+    if (count > ctx->frame_cap) {
+        if (ctx->d_frame) dev_free(ctx, ctx->d_frame);
+        ctx->d_frame = nullptr;
+        ctx->frame_cap = 0;
+        int rc = dev_alloc(ctx, &ctx->d_frame, count);
+        if (rc) return rc;
+        ctx->frame_cap = count;
+    }
+    const int blocks = (int) std::min<size_t>((count / 3 + 255) / 256, 148 * 8);
+    LAUNCH(ctx, k_frame, std::max(blocks, 1), 256, ctx->hp, r0, nrep, (int) fraction_bits, ctx->d_frame);
+    GC_CUDA(ctx, cudaMemcpyAsync(xyz, ctx->d_frame, count * sizeof(float), cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
 }
 
 int gc_debug_noise(gc_ctx *ctx, int32_t replica, int64_t step, float *out)

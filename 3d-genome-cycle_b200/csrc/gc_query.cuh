@@ -339,4 +339,30 @@ __global__ void k_rg2(const __grid_constant__ Params P, int r, int n_ranges, con
     }
 }
 
+// Trajectory frame as the driver stores it (simulation_store::save_positions,
+// SIM/common/simulation_store.cpp:22-32,192-216): every coordinate rounded to
+// `bits` significant binary digits (frexp / nearbyint / ldexp) and packed as f32 x 3.
+// Scaling by powers of two is exact and the scaled mantissa is < 2^(bits + 1), so the
+// FP32 arithmetic below returns the reference's value for FP32 inputs.
+__device__ __forceinline__ float quantize_coord(float v, int bits)
+{
+    int e;
+    const float m = frexpf(v, &e);
+    return ldexpf(rintf(ldexpf(m, bits)), e - bits);
+}
+
+__global__ void __launch_bounds__(256) k_frame(const __grid_constant__ Params P, int r0, int nrep, int bits,
+                                               float *__restrict__ out)
+{
+    GC_PDL_ENTRY();
+    const size_t total = (size_t) nrep * P.n;
+    for (size_t t = (size_t) blockIdx.x * 256 + threadIdx.x; t < total; t += (size_t) gridDim.x * 256) {
+        const int r = r0 + (int) (t / P.n);
+        const float4 p = P.pos[P.st[r].parity][(size_t) r * P.n + (t % P.n)];
+        out[3 * t] = quantize_coord(p.x, bits);
+        out[3 * t + 1] = quantize_coord(p.y, bits);
+        out[3 * t + 2] = quantize_coord(p.z, bits);
+    }
+}
+
 } // namespace gc

@@ -12,6 +12,7 @@ Step counts default to the reference's (SIM/common/simulation_config.hpp:19-24,6
 """
 from __future__ import annotations
 
+import os
 import time
 
 import numpy as np
@@ -31,6 +32,25 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     report = {"beads_interphase": int(design.n), "beads_anaphase": int(md_ana.n),
               "beads_prometaphase": int(md_pro.n),
               "stages": []}
+
+    frames = {"count": 0, "bytes": 0}
+
+    def run_sampled(sys_, n, dt, interval, on_chunk=None):
+        """n steps in chunks of the sampling interval; after each chunk the driver's
+        save_positions: one quantised f32 frame leaves the device (gc_get_frame)."""
+        done = 0
+        if os.environ.get("GC_CYCLE_NO_FRAMES"):        # A/B: no frame output, window-sized chunks
+            interval = max(interval, 10 * interval)
+        while done < n:
+            chunk = min(interval, n - done)
+            sys_.run(chunk, dt, restart=(done == 0))
+            done += chunk
+            if done % interval == 0:
+                f = sys_.get_frame(0, 16)
+                frames["count"] += 1
+                frames["bytes"] += f.nbytes
+            if on_chunk:
+                on_chunk(done)
 
     def timed(name, sys_, n_beads, steps, fn):
         sys_.synchronize()
@@ -53,11 +73,11 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     ga.set_positions(synth.rod_positions(md_ana, mcfg, seed=seed))
     stages.enter_anaphase(ga, ta)
     n = nsteps(mcfg.anaphase_steps)
-    timed("anaphase", ga, md_ana.n, n, lambda: ga.run(n, mcfg.timestep))
+    timed("anaphase", ga, md_ana.n, n, lambda: run_sampled(ga, n, mcfg.timestep, mcfg.sampling_interval))
     stages.enter_telophase(ga, ta)
     ga.set_seeds([seed + 1])
     n = nsteps(mcfg.telophase_steps)
-    timed("telophase", ga, md_ana.n, n, lambda: ga.run(n, mcfg.timestep))
+    timed("telophase", ga, md_ana.n, n, lambda: run_sampled(ga, n, mcfg.timestep, mcfg.sampling_interval))
     x_telo = ga.get_positions()
     ga.close()
 
@@ -78,16 +98,13 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     n = nsteps(icfg.steps)
     window = icfg.sampling_interval * icfg.contactmap_output_window
 
+    def window_end(done):
+        if done % window == 0:              # save_contacts + clear (simulation_driver_interphase.cpp:42-45)
+            report["contact_pairs_last_window"] = int(len(gi.contacts_fetch()))
+            gi.contacts_clear()
+
     def interphase():
-        done, first = 0, True
-        while done < n:
-            chunk = min(window, n - done)
-            gi.run(chunk, icfg.timestep, restart=first)
-            first = False
-            done += chunk
-            if done % window == 0:          # save_contacts + clear (simulation_driver_interphase.cpp:42-45)
-                report["contact_pairs_last_window"] = int(len(gi.contacts_fetch()))
-                gi.contacts_clear()
+        run_sampled(gi, n, icfg.timestep, icfg.sampling_interval, window_end)
     timed("interphase", gi, design.n, n, interphase)
     ctx = gi.get_context()
     report["interphase_end"] = {"time": ctx.time, "semiaxes": list(ctx.semiaxes),
@@ -104,9 +121,11 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     gp.set_seeds([seed + 4])
     gp.set_positions(xp.astype(np.float64))
     n = nsteps(mcfg.prometaphase_steps)
-    timed("prometaphase", gp, md_pro.n, n, lambda: gp.run(n, mcfg.timestep))
+    timed("prometaphase", gp, md_pro.n, n, lambda: run_sampled(gp, n, mcfg.timestep, mcfg.sampling_interval))
     x_meta = gp.get_positions()
     gp.close()
+    report["frames_saved"] = frames["count"]
+    report["frame_bytes"] = frames["bytes"]
     report["next_anaphase_start"] = transitions.transition_cycle(md_pro, md_ana, mcfg, x_meta)
     total_bs = sum(int(r["beads"]) * int(r["steps"]) for r in report["stages"])
     total_s = sum(r["seconds"] for r in report["stages"])

@@ -154,6 +154,11 @@ int gc_set_positions(gc_ctx *ctx, int32_t replica, const double *xyz);
 int gc_get_positions(gc_ctx *ctx, int32_t replica, double *xyz);
 int gc_set_positions_f32(gc_ctx *ctx, int32_t replica, const float *xyz);
 int gc_get_positions_f32(gc_ctx *ctx, int32_t replica, float *xyz);
+/* Trajectory frame as simulation_store::save_positions stores it
+   (SIM/common/simulation_store.cpp:22-32,192-216): every coordinate rounded to
+   fraction_bits significant binary digits (16 in the reference) on the device and
+   returned as packed f32 [n][3]; replica = -1 returns all replicas, [R][n][3]. */
+int gc_get_frame(gc_ctx *ctx, int32_t replica, int32_t fraction_bits, float *xyz);
 /* Philox key per replica (the drivers draw it from mt19937_64(design.seed),
    SIM/stage_interphase/simulation_driver_interphase.cpp:61). */
 int gc_set_seeds(gc_ctx *ctx, const uint64_t *seeds);

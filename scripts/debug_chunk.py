@@ -1,29 +1,17 @@
-import sys
-from pathlib import Path
-ROOT = Path(__file__).resolve().parent.parent
-sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "oracle")); sys.path.insert(0, str(ROOT / "tests"))
+import sys, time
+sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/tests')
 import numpy as np
 from gcpkg import gc_b200
-from helpers import build_pair, small_interphase, stages, synth
-
-d, cfg, x = small_interphase(scale=0.02, radius=0.6)
-kw = dict(contacts=False, wall_ode=False, schedule=False)
-def run(chunks):
-    g, _ = build_pair(lambda n: gc_b200.System(n, 1, 0), d, cfg, x, **kw)
-    g.set_seeds([1234])
-    first = True
-    grids = []
-    for c in chunks:
-        g.run(c, cfg.timestep, restart=first)
-        first = False
-        grids.append(g.debug_grid())
-    return g.get_positions_f32(), grids
-ref = {}
-for m in range(1, 11):
-    ref[m], gr = run((m,))
-    print(m, gr[-1])
-for chunks in ((5, 5), (5, 5), (5, 1), (5, 2), (4, 1), (6, 1), (2, 3, 5)):
-    b, gr = run(chunks)
-    a = ref[sum(chunks)]
-    bad = np.argwhere(a != b)
-    print(chunks, "nd", len(bad), bad[:6].tolist())
+synth, stages = gc_b200.synth, gc_b200.stages
+cfg = synth.InterphaseConfig(); d = synth.make_diploid_design(cfg=cfg)
+x = np.load('/root/repo/tests/golden/interphase_relaxed_60672.npz')
+x = x[x.files[0]] if 'x' not in x.files else x['x']
+g = gc_b200.System(d.n, 1, 0); stages.setup_interphase(g, d, cfg); g.set_positions(x.astype(np.float64)); stages.begin_interphase(g, cfg)
+g.run(1000, cfg.timestep, restart=True); g.synchronize()
+for steps in (1000, 100, 20):
+    t0 = time.perf_counter()
+    for k in range(10): g.run(steps, cfg.timestep, restart=False)
+    g.synchronize(); t1 = time.perf_counter()
+    for k in range(10): g.get_frame(0, 16)
+    t2 = time.perf_counter()
+    print(steps, 'run ms/call', (t1 - t0) * 100, 'us/step', (t1 - t0) / 10 / steps * 1e6, 'frame ms', (t2 - t1) * 100)

@@ -362,3 +362,30 @@ def test_error_reporting():
     assert e.value.code == -4
     with pytest.raises(gc_b200.GcError):
         g.add_bonds([[0, 99]])
+
+
+# ---------------------------------------------------------------------------
+# trajectory output path
+# ---------------------------------------------------------------------------
+def test_quantised_frames_match_the_store_rounding():
+    """gc_get_frame = simulation_store::save_positions' rounding to 16 significant bits
+    (SIM/common/simulation_store.cpp:22-32,192-216, restated in synth.quantize_f32)."""
+    rng = np.random.default_rng(5)
+    n, R = 1000, 3
+    g = gpu(n, R)
+    g.set_bead_attrs(np.ones(n))
+    xs = []
+    for r in range(R):
+        x = (rng.normal(size=(n, 3)) * 10.0 ** rng.integers(-6, 4, size=(n, 1))).astype(np.float32)
+        x[0] = [0.0, -0.0, 1.0]
+        x[1] = [np.float32(1.9999999), np.float32(65535.5 / 65536), -3.0e-30]   # carry, tie, tiny
+        xs.append(x)
+        g.set_positions(x.astype(np.float64), r)
+    for bits in (16, 8, 23):
+        all_frames = g.get_frame(-1, bits)
+        assert all_frames.shape == (R, n, 3) and all_frames.dtype == np.float32
+        for r in range(R):
+            want = synth.quantize_f32(xs[r].astype(np.float64), bits)
+            np.testing.assert_array_equal(all_frames[r], want)
+            np.testing.assert_array_equal(g.get_frame(r, bits), want)
+    g.close()

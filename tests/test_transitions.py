@@ -48,4 +48,4 @@ def test_full_cycle_runs_every_stage():
     assert names == ["anaphase", "telophase", "relaxation", "interphase", "prometaphase"]
     assert all(np.isfinite(r["energy_per_bead"]) for r in rep["stages"])
     assert rep["next_anaphase_start"].shape[0] == rep["beads_anaphase"]
-    assert rep["interphase_end"]["core_scale"] > 0.5
+    assert rep["interphase_end"]["core_scale"] > 0.5 and rep["frames_saved"] >= 0
