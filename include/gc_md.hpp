@@ -276,6 +276,16 @@ public:
         return ijv;
     }
 
+    // simulation_store::save_positions' payload: the frame rounded to `fraction_bits`
+    // significant bits, packed f32 [n][3] (SIM/common/simulation_store.cpp:192-216)
+    std::vector<float> quantized_frame(int replica = 0, int fraction_bits = 16)
+    {
+        push();
+        std::vector<float> xyz(3 * static_cast<std::size_t>(particle_count()));
+        check(gc_get_frame(ctx(), replica, fraction_bits, xyz.data()));
+        return xyz;
+    }
+
     // ---- evaluation -------------------------------------------------------------------
     scalar compute_potential_energy(int replica = 0, std::uint32_t mask = GC_MASK_ALL)
     {
