@@ -224,7 +224,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         // resident blocks per SM of k_pair_cells (60 registers, 26 KB shared memory:
         // __launch_bounds__(128, GC_CELL_MINBLOCKS)); measured best at 8, profiles/r1_notes.md
         int per_sm = GC_CELL_MINBLOCKS;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells, CW * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells<false>, CW * 32, 0);
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
         ctx->pdl = getenv("GC_NO_PDL") == nullptr;
@@ -823,7 +823,11 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
 // one force evaluation (+ update when fused) for every replica
 void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
 {
-    LAUNCH(ctx, k_pair_cells, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    if (ctx->hp.pair.mode == PAIR_PLAIN) {
+        LAUNCH(ctx, k_pair_cells<true>, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    } else {
+        LAUNCH(ctx, k_pair_cells<false>, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    }
     dim3 gf = bead_grid(ctx, BS);
     const int gr = ctx->n_rep;
     if (mode == STEP_FUSED) {
@@ -1532,7 +1536,11 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     }
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
-    LAUNCH(ctx, k_pair_cells, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+    if (ctx->hp.pair.mode == PAIR_PLAIN) {
+        LAUNCH(ctx, k_pair_cells<true>, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+    } else {
+        LAUNCH(ctx, k_pair_cells<false>, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+    }
     const int owned = P.own_hi - P.own_lo;
     LAUNCH(ctx, k_finish<STEP_FUSED>, dim3(std::max((owned + BS - 1) / BS, 1), 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);

@@ -24,6 +24,8 @@
 // result is bit-reproducible and independent of the queue order.
 #pragma once
 
+#include <cstddef>
+
 #include "gc_step.cuh"
 
 namespace gc {
@@ -40,6 +42,9 @@ constexpr int CW = 4;                    // warps per block
 #endif
 constexpr int kPackUnroll = GC_PACK_UNROLL;   // candidate pairs in flight per lane
 constexpr int CCAP = GC_CCAP;            // candidates per tile chunk
+// kRecip[d] = 65536 / d + 1: x / d == (x * kRecip[d]) >> 16 for x * d < 65536 (lane splits,
+// slice counts and tile lengths are all far below); index 0 is unused
+__constant__ unsigned int kRecip[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
 constexpr int CHMAX = 16;                // home beads per pass
 constexpr int CGROUP = 2 * CHMAX;        // home beads per staged tile (two passes)
 
@@ -87,7 +92,9 @@ __device__ __forceinline__ void cell_pass(const CellWarpSmem &sm, int nt, int S,
                                           float4 me, float Ai, float Bi, float kA2, float kB2,
                                           float &fx, float &fy, float &fz)
 {
-    const int full = (nt >> 1) / S;      // iterations in which every slice has a whole pair
+    // iterations in which every slice has a whole pair: (nt / 2) / S by reciprocal
+    // multiplication (exact for nt / 2 <= 2047, S <= 32)
+    const int full = (int) (((unsigned) (nt >> 1) * kRecip[S]) >> 16);
     const float2 xi = make_float2(me.x, me.x), yi = make_float2(me.y, me.y), zi = make_float2(me.z, me.z);
     const float2 Ai2 = make_float2(Ai, Ai), Bi2 = make_float2(Bi, Bi);
     const float2 nkA = make_float2(-kA2, -kA2), kB = make_float2(kB2, kB2), one = make_float2(1.0f, 1.0f);
@@ -136,6 +143,7 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
     }
 }
 
+template<bool PLAIN>
 __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
@@ -157,8 +165,14 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
 
     const int M = P.cells_per_cut;
     const int side = 2 * M + 1, nrows = side * side;
-    const bool plain = P.pair.mode == PAIR_PLAIN;
+    constexpr bool plain = PLAIN;          // one soft core, no A/B mixing (mitotic stages)
     CellWarpSmem &sm = s_warp[warp];
+    // tx, ty, tz, tA, tB are consecutive arrays of CCAP floats (static_assert below)
+    const unsigned tile_addr = (unsigned) __cvta_generic_to_shared(sm.tx);
+    static_assert(offsetof(CellWarpSmem, ty) == sizeof(float2) * (CCAP / 2) &&
+                  offsetof(CellWarpSmem, tz) == 2 * sizeof(float2) * (CCAP / 2) &&
+                  offsetof(CellWarpSmem, tA) == 3 * sizeof(float2) * (CCAP / 2) &&
+                  offsetof(CellWarpSmem, tB) == 4 * sizeof(float2) * (CCAP / 2), "tile layout");
 
     // Blocks are not tied to a replica: every warp works through the queues of all
     // replicas round-robin, starting at a different one, so an ensemble is balanced
@@ -215,9 +229,10 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
             const int ng = min(CGROUP, nhome - g0);
             // pass a: beads [g0, g0 + Ha), pass b: beads [g0 + Ha, g0 + ng)
             const int Ha = min(CHMAX, ng), Hb = ng - Ha;
-            const int Sa = 32 / Ha, Sb = Hb > 0 ? 32 / Hb : 1;
-            const int sa = (lane * (65536 / Ha + 1)) >> 16, ha = lane - sa * Ha;
-            const int sb = Hb > 0 ? (lane * (65536 / Hb + 1)) >> 16 : 0;
+            const unsigned ra = kRecip[Ha], rb = kRecip[max(Hb, 1)];
+            const int Sa = (int) ((32u * ra) >> 16), Sb = Hb > 0 ? (int) ((32u * rb) >> 16) : 1;
+            const int sa = (int) (((unsigned) lane * ra) >> 16), ha = lane - sa * Ha;
+            const int sb = Hb > 0 ? (int) (((unsigned) lane * rb) >> 16) : 0;
             const int hb = Hb > 0 ? lane - sb * Hb : 0;
             const float4 ma = __ldg(&sp[h0 + g0 + ha]);
             const int ib = Hb > 0 ? g0 + Ha + hb : g0;         // pass b idles on bead g0
@@ -234,24 +249,23 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
             // ---- 2. stage: flattened, coalesced within each row, culled, compacted --------
             // The loads of the next 32 candidates are issued before the current 32 are
             // tested and stored (and before the home beads' bounding box is reduced).
+            // (tail lanes re-read the last candidate and are masked out of the ballot, so the
+            // loop body has no predicated blocks)
             int kin = 0, row = 0, end = sm.row_off[1], shift = sm.row_shift[0];
-            float4 qn = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 qn;
             float2 abn = make_float2(0.f, 0.f);
-            bool vn = false;
+            const int last = total - 1;
             auto fetch = [&](int k0) {
-                const int k = k0 + lane;
-                vn = k < total;
-                if (vn) {
-                    if (k >= end) {
-                        do {
-                            row++;
-                            end = sm.row_off[row + 1];
-                        } while (k >= end);
-                        shift = sm.row_shift[row];
-                    }
-                    qn = __ldg(&sp[k + shift]);
-                    if (!plain) abn = __ldg(&sab[k + shift]);
+                const int k = min(k0 + lane, last);
+                if (k >= end) {
+                    do {
+                        row++;
+                        end = sm.row_off[row + 1];
+                    } while (k >= end);
+                    shift = sm.row_shift[row];
                 }
+                qn = __ldg(&sp[k + shift]);
+                if (!plain) abn = __ldg(&sab[k + shift]);
             };
             fetch(0);
             // Bounding box of this group's home beads: a candidate further than the cutoff
@@ -270,9 +284,9 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
             }
             int nt = 0;
             while (kin < total) {
-                float4 q = qn;
+                const float4 q = qn;
                 const float2 ab = abn;
-                const bool v = vn;
+                const bool v = kin + lane < total;
                 kin += 32;
                 if (kin < total) fetch(kin);
                 const float ex = fmaxf(fmaxf(blo[0] - q.x, q.x - bhi[0]), 0.0f);
@@ -281,12 +295,14 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
                 const bool keep = v && fmaf(ex, ex, fmaf(ey, ey, ez * ez)) <= cull2;
                 const unsigned m = __ballot_sync(0xffffffffu, keep);
                 if (keep) {
-                    const int d = nt + __popc(m & lt_mask);
-                    reinterpret_cast<float *>(sm.tx)[d] = q.x;
-                    reinterpret_cast<float *>(sm.ty)[d] = q.y;
-                    reinterpret_cast<float *>(sm.tz)[d] = q.z;
-                    reinterpret_cast<float *>(sm.tA)[d] = plain ? hA : hA * ab.x;
-                    reinterpret_cast<float *>(sm.tB)[d] = plain ? 0.0f : hB * ab.y;
+                    // explicit shared-space stores: one address, five immediate offsets
+                    const unsigned a = tile_addr + 4u * (unsigned) (nt + __popc(m & lt_mask));
+                    constexpr unsigned kStride = (unsigned) (sizeof(float2) * (CCAP / 2));
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(q.x) : "memory");
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + kStride), "f"(q.y) : "memory");
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 2 * kStride), "f"(q.z) : "memory");
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 3 * kStride), "f"(plain ? hA : hA * ab.x) : "memory");
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 4 * kStride), "f"(plain ? 0.0f : hB * ab.y) : "memory");
                 }
                 nt += __popc(m);
                 if (nt > CCAP - 32 || kin >= total) {          // tile full or input exhausted

@@ -437,7 +437,7 @@ def run_b200_arm(args):
                            f"scalar {fp32_scalar:.2f} and packed {fp32_packed:.2f} TFLOP/s",
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_pair_cells launch from the
             # committed ncu --set full capture of this workload (8 cells, relaxed state)
-            "traffic": 13.48e6 if (R == 8 and args.scale == 1.0 and name == "k_pair_cells") else None,
+            "traffic": 13.48e6 if (R == 8 and args.scale == 1.0 and name.startswith("k_pair_cells")) else None,
             "traffic_source": "profiles/r1_pair_cells_v4_sparse_ncu_summary.txt (13.48 MB read, 1.3 KB written "
                               "per launch; algorithmic 32 B x R x N = %.2f MB)" % (32 * R * n / 1e6),
             "executed": {"pair_evaluations_per_launch": executed_pairs, "flop_per_pair_evaluation": FLOP_PER_PAIR,
