@@ -77,6 +77,9 @@ struct gc_ctx {
     // CUDA-graph replay of the fixed-timestep step loop (gc_run)
     cudaGraphExec_t step_graph = nullptr;
     int step_graph_steps = 0;       // steps per replay
+    // small systems (<= SMALL_MAX_BEADS beads, default cell budget): one-block rebuild,
+    // fused with the step epilogue in fixed-dt runs (gc_kernels.cuh, gc_step.cuh)
+    bool small = false;
     long long step_graph_launches = 0;
     Params step_graph_hp;           // kernel arguments baked into the graph
     long long step_graph_interval = -1;
@@ -228,6 +231,8 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
         ctx->pdl = getenv("GC_NO_PDL") == nullptr;
+        ctx->small = n_beads <= SMALL_MAX_BEADS && P.ncell_max <= SMALL_MAX_CELLS &&
+                     getenv("GC_NO_SMALL") == nullptr;
     }
     P.skin = 0.0f;
     P.kT = 1.0f;
@@ -780,8 +785,15 @@ int plan_and_rebuild(gc_ctx *ctx, double radius_override)
     return GC_OK;
 }
 
+// small path: one block per replica instead of the four kernels
+inline bool small_path(const gc_ctx *ctx) { return ctx->small && !ctx->hp.decomp; }
+
 void launch_rebuild(gc_ctx *ctx)
 {
+    if (small_path(ctx)) {
+        LAUNCH(ctx, k_rebuild_small, ctx->n_rep, SMALL_BS, ctx->hp);
+        return;
+    }
     dim3 g = bead_grid(ctx, 256);
     LAUNCH(ctx, k_count, g, 256, ctx->hp);
     LAUNCH(ctx, k_scan, dim3(ctx->hp.scan_blocks, ctx->n_rep), SCAN_BS, ctx->hp);
@@ -821,7 +833,8 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
 }
 
 // one force evaluation (+ update when fused) for every replica
-void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
+// fuse_rebuild (fixed dt, small path): the epilogue also builds the NEXT step's cell list
+void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled, bool fuse_rebuild = false)
 {
     if (ctx->hp.pair.mode == PAIR_PLAIN) {
         LAUNCH(ctx, k_pair_cells<true>, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
@@ -832,7 +845,11 @@ void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled)
     const int gr = ctx->n_rep;
     if (mode == STEP_FUSED) {
         LAUNCH(ctx, k_finish<STEP_FUSED>, gf, BS, ctx->hp, mask, use_enabled);
-        LAUNCH(ctx, k_finalize_step, gr, 32, ctx->hp, 0);
+        if (fuse_rebuild) {
+            LAUNCH(ctx, k_finalize_rebuild, gr, SMALL_BS, ctx->hp);
+        } else {
+            LAUNCH(ctx, k_finalize_step, gr, 32, ctx->hp, 0);
+        }
     } else {
         LAUNCH(ctx, k_finish<STEP_FORCE>, gf, BS, ctx->hp, mask, use_enabled);
         LAUNCH(ctx, k_finalize_force, gr, 32, ctx->hp);
@@ -874,10 +891,11 @@ bool ensure_step_graph(gc_ctx *ctx, long long interval)
         cudaGetLastError();
         return false;
     }
+    const bool fuse = small_path(ctx);    // the cell list is current when the block starts
     for (int k = 0; k < B; k++) {
-        launch_rebuild(ctx);
+        if (!fuse) launch_rebuild(ctx);
         if (k == 0 && interval > 0) launch_contact_update(ctx);
-        launch_step(ctx, STEP_FUSED, 0u, 1);
+        launch_step(ctx, STEP_FUSED, 0u, 1, fuse);
     }
     cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
     ctx->step_graph_launches = ctx->launches - before;
@@ -964,6 +982,9 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     const dim3 g = bead_grid(ctx, BS);
     const bool graphable = !adaptive && !c->noise && c->steps >= 64 && ensure_step_graph(ctx, interval);
     const int B = graphable ? ctx->step_graph_steps : 0;
+    // small path, fixed dt: every step's epilogue leaves the cell list of the next step
+    const bool fuse = small_path(ctx) && !adaptive;
+    if (fuse && c->steps > 0) launch_rebuild(ctx);
     for (long long i = 0; i < c->steps;) {
         // a whole block, aligned to the contact cadence (the block opens with the contact
         // update of the step just finished)
@@ -976,7 +997,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
             i += B;
             continue;
         }
-        launch_rebuild(ctx);
+        if (!fuse) launch_rebuild(ctx);
         // contact update of the driver callback for the step just finished
         // (SIM/stage_interphase/simulation_driver_interphase.cpp:38-40)
         if (interval > 0 && ctx->run_step > 0 && ctx->run_step % interval == 0 && i > 0) {
@@ -987,7 +1008,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
             LAUNCH(ctx, k_integrate, g, BS, ctx->hp);
             LAUNCH(ctx, k_finalize_step, ctx->n_rep, 32, ctx->hp, 1);
         } else {
-            launch_step(ctx, STEP_FUSED, 0u, 1);
+            launch_step(ctx, STEP_FUSED, 0u, 1, fuse);
         }
         ctx->run_step++;
         ctx->parity ^= 1;
@@ -995,7 +1016,7 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     }
     // the callback of the last step of this chunk
     if (interval > 0 && c->steps > 0 && ctx->run_step % interval == 0) {
-        launch_rebuild(ctx);
+        if (!fuse) launch_rebuild(ctx);
         launch_contact_update(ctx);
     }
     return check_device_errors(ctx);

@@ -317,14 +317,10 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
     P.members[(size_t) r * P.n + s] = i;
 }
 
-__global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P)
+// Sorted slot of member entry `s`: rank inside the cell = ascending bead id, so the sorted
+// order (and with it every force sum) does not depend on the order of k_fill's atomics.
+__device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r, int s)
 {
-    GC_PDL_ENTRY();
-    int r = blockIdx.y;
-    RepState &st = P.st[r];
-    if (!st.need_rebuild) return;
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= P.n) return;
     size_t ro = (size_t) r * P.n;
     const int *members = P.members + ro;
     int idx = members[s];
@@ -356,6 +352,110 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P
     if (P.skin > 0.0f) P.sref[ro + dst] = p;
     P.scell[ro + dst] = c;
     P.sab[ro + dst] = P.ab[idx];
+}
+
+__global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    int r = blockIdx.y;
+    RepState &st = P.st[r];
+    if (!st.need_rebuild) return;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.n) return;
+    gather_slot(P, st, r, s);
+}
+
+// ---------------------------------------------------------------------------
+// Small systems (the ~600 / ~1,200-bead mitotic stages): the four rebuild kernels are
+// pure launch latency there, so ONE block per replica does count -> scan -> fill ->
+// gather with block barriers in between.  Same data structures, same sorted order
+// (rank = ascending bead id), hence bit-identical forces.
+// ---------------------------------------------------------------------------
+constexpr int SMALL_BS = 1024;
+constexpr int SMALL_MAX_BEADS = 4096;
+constexpr int SMALL_MAX_CELLS = 32768;
+
+// executed by all SMALL_BS threads of a block; sh: 32 ints of shared memory
+__device__ inline void block_rebuild(const Params &P, int r, int *sh)
+{
+    RepState &st = P.st[r];
+    if (!st.need_rebuild) return;                            // block-uniform
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const size_t ro = (size_t) r * P.n;
+    int *count = P.cell_count + (size_t) r * P.ncell_max;
+    int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+    const float4 *pos = P.pos[st.parity] + ro;
+    const int ncell = st.ncell;
+    if (tid == 0) { st.n_used_cells = 0; st.n_light_cells = 0; }
+
+    // 1. cell of every bead, histogram (counts are zero on entry: gather_slot's invariant)
+    for (int i = tid; i < P.n; i += SMALL_BS) {
+        const int c = cell_index(st, pos[i], P.cells_per_cut);
+        P.cell_of[ro + i] = c;
+        atomicAdd(&count[c], 1);
+    }
+    __syncthreads();
+
+    // 2. exclusive scan in tiles of 4 cells per thread, running carry; counts back to 0
+    int carry = 0;
+    for (int base = 0; base < ncell; base += SMALL_BS * 4) {
+        const int c = base + tid * 4;
+        int4 v = make_int4(0, 0, 0, 0);
+        if (c + 3 < ncell) {
+            v = *reinterpret_cast<const int4 *>(count + c);
+            *reinterpret_cast<int4 *>(count + c) = make_int4(0, 0, 0, 0);
+        } else {
+            if (c < ncell) { v.x = count[c]; count[c] = 0; }
+            if (c + 1 < ncell) { v.y = count[c + 1]; count[c + 1] = 0; }
+            if (c + 2 < ncell) { v.z = count[c + 2]; count[c + 2] = 0; }
+        }
+        const int tsum = v.x + v.y + v.z + v.w;
+        int x = tsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) sh[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int w = sh[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            sh[lane] = w;                                    // inclusive over warps
+        }
+        __syncthreads();
+        int e = carry + (wid ? sh[wid - 1] : 0) + x - tsum;
+        carry += sh[SMALL_BS / 32 - 1];
+        if (c < ncell) start[c] = e;
+        e += v.x;
+        if (c + 1 < ncell) start[c + 1] = e;
+        e += v.y;
+        if (c + 2 < ncell) start[c + 2] = e;
+        e += v.z;
+        if (c + 3 < ncell) start[c + 3] = e;
+        __syncthreads();                                     // sh is reused by the next tile
+    }
+    if (tid == 0) start[ncell] = carry;
+    __syncthreads();
+
+    // 3. members of every cell (arbitrary order), 4. sorted copies (deterministic order)
+    for (int i = tid; i < P.n; i += SMALL_BS) {
+        const int c = P.cell_of[ro + i];
+        P.members[ro + start[c] + atomicAdd(&count[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int s = tid; s < P.n; s += SMALL_BS) gather_slot(P, st, r, s);
+}
+
+__global__ void __launch_bounds__(SMALL_BS) k_rebuild_small(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    __shared__ int sh[32];
+    block_rebuild(P, blockIdx.x, sh);
 }
 
 } // namespace gc

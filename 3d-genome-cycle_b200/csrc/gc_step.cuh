@@ -553,6 +553,31 @@ __global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Pa
     repstate_store(P.st[r], s, lane);
 }
 
+// Small systems, fixed dt: the epilogue of step n and the cell list of step n + 1 in one
+// launch (one SMALL_BS block per replica; warp 0 is k_finalize_step, then the whole block
+// re-bins the positions just written).  A mitotic-stage step is then 3 launches
+// (k_pair_cells, k_finish, this) instead of 7.
+__global__ void __launch_bounds__(SMALL_BS) k_finalize_rebuild(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    __shared__ RepState s;
+    __shared__ int sh[32];
+    const int r = blockIdx.x;
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        repstate_load(s, P.st[r], lane);
+        if (lane == 0) {
+            finalize_stats(s);
+            finalize_step(P, s, P.dt_cfg);
+        }
+        __syncwarp();
+        refresh_consts_item(P, s, lane);
+        repstate_store(P.st[r], s, lane);
+    }
+    __syncthreads();                       // the new RepState is visible to the whole block
+    block_rebuild(P, r, sh);
+}
+
 // after k_finish<STEP_FORCE>: wall statistics and the adaptive time step
 // (MD/simulation/detail/brownian_timestepper.hpp:109-136: global minimum)
 __global__ void __launch_bounds__(32) k_finalize_force(const __grid_constant__ Params P)

@@ -315,6 +315,75 @@ def test_run_is_deterministic_and_chunkable():
     assert np.array_equal(out[0][1], out[2][1])
 
 
+def _with_env(name, value, fn):
+    import os
+    old = os.environ.get(name)
+    if value is None:
+        os.environ.pop(name, None)
+    else:
+        os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        if old is None:
+            os.environ.pop(name, None)
+        else:
+            os.environ[name] = old
+
+
+@pytest.mark.parametrize("replicas", [1, 3])
+def test_small_system_path_is_bit_identical_to_the_four_kernel_rebuild(replicas):
+    """<= 4,096 beads: one block per replica rebuilds the cell list (k_rebuild_small) and, in
+    fixed-dt runs, does so in the step epilogue (k_finalize_rebuild: 3 launches per step
+    instead of 7).  Same sorted order => identical bits; GC_NO_SMALL=1 selects the
+    four-kernel path at gc_create."""
+    d = synth.make_diploid_design(scale=0.3)
+    mcfg = synth.MitoticConfig()
+    md = synth.make_mitotic_design(d, mcfg, sisters=True)
+    x = (np.random.default_rng(5).normal(size=(md.n, 3)) * 1.5).astype(np.float32).astype(np.float64)
+
+    def prometaphase():
+        g = gpu(md.n, replicas)
+        stages.setup_prometaphase(g, md, mcfg)
+        g.set_positions(x)
+        g.set_seeds(np.arange(7, 7 + replicas, dtype=np.uint64))
+        f0 = g.compute_force()
+        pairs = g.neighbor_pairs(0.3)
+        launches0 = g.launch_count()
+        g.run(300, mcfg.timestep)                 # plain launches, then graph replays
+        per_step = (g.launch_count() - launches0) / 300
+        g.run(37, mcfg.timestep, restart=False)   # ragged chunk
+        out = (f0, pairs, np.stack([g.get_positions_f32(r) for r in range(replicas)]),
+               g.compute_energy(), per_step)
+        g.close()
+        return out
+
+    small = _with_env("GC_NO_SMALL", None, prometaphase)
+    plain = _with_env("GC_NO_SMALL", "1", prometaphase)
+    for a, b in zip(small[:4], plain[:4]):
+        assert np.array_equal(a, b)
+    assert small[4] < 3.3 and plain[4] > 6.9      # launches per step
+
+    # interphase force set (wall ODE, schedule, contact map every 20 steps), adaptive and fixed dt
+    di, cfg, xi = small_interphase(scale=0.02, radius=0.6)
+
+    def interphase():
+        g, _ = build_pair(gpu, di, cfg, xi)
+        g.set_seeds([99])
+        g.run(30, cfg.timestep, spacestep=cfg.relaxation_spacestep)
+        stages.interphase_callback0(g, cfg)
+        g.run(130, cfg.timestep)
+        out = (g.get_positions_f32(), g.contacts_fetch(), np.array(g.get_context().semiaxes))
+        g.close()
+        return out
+
+    assert di.n <= 4096
+    small = _with_env("GC_NO_SMALL", None, interphase)
+    plain = _with_env("GC_NO_SMALL", "1", interphase)
+    for a, b in zip(small, plain):
+        assert np.array_equal(a, b)
+
+
 def test_philox_stream_is_standard_normal():
     n = 200000
     g = gpu(n)
