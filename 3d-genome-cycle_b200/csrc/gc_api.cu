@@ -85,6 +85,14 @@ struct gc_ctx {
     long long step_graph_interval = -1;
     double skin = 0.0;
     int tile_grid_x = 1;        // blocks per replica of the pair kernel
+    // Replica groups of the step graph: the replicas are independent trajectories, so the
+    // graph runs them as `groups` parallel branches (one capture stream each).  The
+    // latency-bound kernels of one group (cell scan, epilogue, count / fill) then overlap
+    // the pair kernel of the others instead of leaving the GPU idle.
+    int groups = 1;
+    int group_grid_x = 1;       // pair-kernel blocks of one group
+    std::vector<cudaStream_t> group_streams;
+    std::vector<cudaEvent_t> group_events;   // [0] fork, [1 + g] join of group g
 
 
     // result of the last contact query (sorted keys / counts on the device)
@@ -231,6 +239,14 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
         ctx->pdl = getenv("GC_NO_PDL") == nullptr;
+        // replica groups (see gc_ctx): up to 8 branches; their pair kernels share the SMs,
+        // ~16 blocks per SM in total (measured: profiles/r1_notes.md)
+        int groups = std::min(n_replicas, 8);
+        if (const char *env = getenv("GC_GROUPS")) groups = std::max(1, std::min(atoi(env), n_replicas));
+        int per_group = std::max(1, std::min(per_sm, 16 / std::max(groups, 1)));
+        if (const char *env = getenv("GC_GROUP_BLOCKS_PER_SM")) per_group = std::max(1, atoi(env));
+        ctx->groups = std::max(groups, 1);
+        ctx->group_grid_x = ctx->groups > 1 ? sms * per_group : ctx->tile_grid_x;
         ctx->small = n_beads <= SMALL_MAX_BEADS && P.ncell_max <= SMALL_MAX_CELLS &&
                      getenv("GC_NO_SMALL") == nullptr;
     }
@@ -292,6 +308,8 @@ int gc_destroy(gc_ctx *ctx)
     }
     for (void *p : ctx->allocs) cudaFree(p);
     if (ctx->step_graph) cudaGraphExecDestroy(ctx->step_graph);
+    for (cudaStream_t gs : ctx->group_streams) cudaStreamDestroy(gs);
+    for (cudaEvent_t ge : ctx->group_events) cudaEventDestroy(ge);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return GC_OK;
@@ -861,6 +879,50 @@ void launch_contact_update(gc_ctx *ctx)
     LAUNCH(ctx, k_contact_cells, ctx->tile_grid_x, CW * 32, ctx->hp, (int) RADIUS_CONTACT_PREV);
 }
 
+// The kernel arguments of replicas [r0, r0 + nr): every per-replica array starts at r0, so
+// the kernels (which index replicas from 0) run unchanged on the sub-range.
+Params params_window(const Params &P, int r0, int nr)
+{
+    Params W = P;
+    const size_t o = (size_t) r0 * (size_t) P.n;
+    W.n_rep = nr;
+    for (int k = 0; k < 2; k++) { W.pos[k] += o; W.spos[k] += o; }
+    W.sref += o;
+    W.scell += o;
+    W.sab += o;
+    W.members += o;
+    W.cell_of += o;
+    W.cell_list += o;
+    W.force += o;
+    W.pforce += o;
+    W.cell_count += (size_t) r0 * P.ncell_max;
+    W.cell_start += (size_t) r0 * (P.ncell_max + 1);
+    W.scan_status += (size_t) r0 * P.scan_blocks;
+    W.st += r0;
+    if (W.noise) W.noise += (size_t) r0 * (size_t) P.noise_steps * (size_t) P.n * 3;
+    if (W.contact.bucket) W.contact.bucket += o * (size_t) P.contact.bucket_slots;
+    if (W.contact.keys) W.contact.keys += (size_t) r0 * P.contact.capacity;
+    if (W.contact.vals) W.contact.vals += (size_t) r0 * P.contact.capacity;
+    if (W.contact.used) W.contact.used += r0;
+    return W;
+}
+
+bool ensure_group_streams(gc_ctx *ctx)
+{
+    const int G = ctx->groups;
+    while ((int) ctx->group_streams.size() < G) {
+        cudaStream_t s = nullptr;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return false;
+        ctx->group_streams.push_back(s);
+    }
+    while ((int) ctx->group_events.size() < G + 1) {
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return false;
+        ctx->group_events.push_back(e);
+    }
+    return true;
+}
+
 void drop_step_graph(gc_ctx *ctx)
 {
     if (ctx->step_graph) cudaGraphExecDestroy(ctx->step_graph);
@@ -892,10 +954,38 @@ bool ensure_step_graph(gc_ctx *ctx, long long interval)
         return false;
     }
     const bool fuse = small_path(ctx);    // the cell list is current when the block starts
-    for (int k = 0; k < B; k++) {
-        if (!fuse) launch_rebuild(ctx);
-        if (k == 0 && interval > 0) launch_contact_update(ctx);
-        launch_step(ctx, STEP_FUSED, 0u, 1, fuse);
+    auto record_block = [&]() {
+        for (int k = 0; k < B; k++) {
+            if (!fuse) launch_rebuild(ctx);
+            if (k == 0 && interval > 0) launch_contact_update(ctx);
+            launch_step(ctx, STEP_FUSED, 0u, 1, fuse);
+        }
+    };
+    const int G = (ctx->groups > 1 && ensure_group_streams(ctx)) ? ctx->groups : 1;
+    if (G > 1) {
+        // fork: one branch per replica group, each on its own capture stream with the
+        // kernel arguments windowed to its replicas; join back into the launch stream
+        const Params full = ctx->hp;
+        const int R = ctx->n_rep, grid_full = ctx->tile_grid_x;
+        cudaStream_t main_stream = ctx->stream;
+        cudaEventRecord(ctx->group_events[0], main_stream);
+        for (int g = 0; g < G; g++) {
+            const int r0 = (int) ((long long) R * g / G), r1 = (int) ((long long) R * (g + 1) / G);
+            cudaStreamWaitEvent(ctx->group_streams[g], ctx->group_events[0], 0);
+            ctx->stream = ctx->group_streams[g];
+            ctx->hp = params_window(full, r0, r1 - r0);
+            ctx->n_rep = r1 - r0;
+            ctx->tile_grid_x = ctx->group_grid_x;
+            record_block();
+            cudaEventRecord(ctx->group_events[1 + g], ctx->group_streams[g]);
+        }
+        ctx->stream = main_stream;
+        ctx->hp = full;
+        ctx->n_rep = R;
+        ctx->tile_grid_x = grid_full;
+        for (int g = 0; g < G; g++) cudaStreamWaitEvent(main_stream, ctx->group_events[1 + g], 0);
+    } else {
+        record_block();
     }
     cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
     ctx->step_graph_launches = ctx->launches - before;

@@ -362,7 +362,8 @@ def test_small_system_path_is_bit_identical_to_the_four_kernel_rebuild(replicas)
     plain = _with_env("GC_NO_SMALL", "1", prometaphase)
     for a, b in zip(small[:4], plain[:4]):
         assert np.array_equal(a, b)
-    assert small[4] < 3.3 and plain[4] > 6.9      # launches per step
+    # launches per step and replica group (the graph has one branch per replica here)
+    assert small[4] / replicas < 3.3 and plain[4] > 2.2 * small[4]
 
     # interphase force set (wall ODE, schedule, contact map every 20 steps), adaptive and fixed dt
     di, cfg, xi = small_interphase(scale=0.02, radius=0.6)
@@ -382,6 +383,36 @@ def test_small_system_path_is_bit_identical_to_the_four_kernel_rebuild(replicas)
     plain = _with_env("GC_NO_SMALL", "1", interphase)
     for a, b in zip(small, plain):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("scale,replicas", [(0.02, 5), (0.1, 3), (0.1, 11)])
+def test_replica_groups_of_the_step_graph_change_nothing(scale, replicas):
+    """The step graph runs the replicas as parallel branches (one capture stream per group,
+    kernel arguments windowed to the group's replicas).  GC_GROUPS=1 is the single-branch
+    graph: positions, contact triples and wall state must be bit-identical."""
+    d, cfg, x = small_interphase(scale=scale, radius=0.6 if scale < 0.05 else 1.0)
+
+    def run():
+        g = gpu(d.n, replicas)
+        stages.setup_interphase(g, d, cfg)
+        g.set_positions(x)
+        g.set_seeds(np.arange(11, 11 + replicas, dtype=np.uint64))
+        stages.interphase_callback0(g, cfg)
+        g.run(150, cfg.timestep)
+        g.run(90, cfg.timestep, restart=False)
+        out = []
+        for r in range(replicas):
+            out += [g.get_positions_f32(r), g.contacts_fetch(r), np.array(g.get_context(r).semiaxes)]
+        g.close()
+        return out
+
+    grouped = _with_env("GC_GROUPS", None, run)
+    single = _with_env("GC_GROUPS", "1", run)
+    assert len(grouped[1]) > 0
+    for a, b in zip(grouped, single):
+        assert np.array_equal(a, b)
+    # replicas differ from one another (different seeds), i.e. the windows are distinct
+    assert not np.array_equal(grouped[0], grouped[3])
 
 
 def test_philox_stream_is_standard_normal():
