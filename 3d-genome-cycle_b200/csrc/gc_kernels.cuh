@@ -396,20 +396,21 @@ __device__ inline void block_rebuild(const Params &P, int r, int *sh)
     }
     __syncthreads();
 
-    // 2. exclusive scan in tiles of 4 cells per thread, running carry; counts back to 0
-    int carry = 0;
-    for (int base = 0; base < ncell; base += SMALL_BS * 4) {
-        const int c = base + tid * 4;
-        int4 v = make_int4(0, 0, 0, 0);
-        if (c + 3 < ncell) {
-            v = *reinterpret_cast<const int4 *>(count + c);
-            *reinterpret_cast<int4 *>(count + c) = make_int4(0, 0, 0, 0);
-        } else {
-            if (c < ncell) { v.x = count[c]; count[c] = 0; }
-            if (c + 1 < ncell) { v.y = count[c + 1]; count[c + 1] = 0; }
-            if (c + 2 < ncell) { v.z = count[c + 2]; count[c + 2] = 0; }
+    // 2. exclusive scan, counts back to 0: every thread owns `per` consecutive cells (a
+    //    multiple of 4, read as int4; the second pass re-reads its own lines from L1), so
+    //    the whole scan costs two block barriers whatever the cell count
+    {
+        const int per = (((ncell + SMALL_BS - 1) / SMALL_BS) + 3) & ~3;
+        const int c0 = min(tid * per, ncell), c1 = min(c0 + per, ncell);
+        int tsum = 0;
+        for (int c = c0; c < c1; c += 4) {
+            if (c + 3 < c1) {
+                const int4 v = *reinterpret_cast<const int4 *>(count + c);
+                tsum += v.x + v.y + v.z + v.w;
+            } else {
+                for (int k = c; k < c1; k++) tsum += count[k];
+            }
         }
-        const int tsum = v.x + v.y + v.z + v.w;
         int x = tsum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -428,18 +429,28 @@ __device__ inline void block_rebuild(const Params &P, int r, int *sh)
             sh[lane] = w;                                    // inclusive over warps
         }
         __syncthreads();
-        int e = carry + (wid ? sh[wid - 1] : 0) + x - tsum;
-        carry += sh[SMALL_BS / 32 - 1];
-        if (c < ncell) start[c] = e;
-        e += v.x;
-        if (c + 1 < ncell) start[c + 1] = e;
-        e += v.y;
-        if (c + 2 < ncell) start[c + 2] = e;
-        e += v.z;
-        if (c + 3 < ncell) start[c + 3] = e;
-        __syncthreads();                                     // sh is reused by the next tile
+        int e = (wid ? sh[wid - 1] : 0) + x - tsum;
+        for (int c = c0; c < c1; c += 4) {
+            if (c + 3 < c1) {
+                const int4 v = *reinterpret_cast<const int4 *>(count + c);
+                *reinterpret_cast<int4 *>(count + c) = make_int4(0, 0, 0, 0);
+                int4 o4;
+                o4.x = e; e += v.x;
+                o4.y = e; e += v.y;
+                o4.z = e; e += v.z;
+                o4.w = e; e += v.w;
+                start[c] = o4.x; start[c + 1] = o4.y; start[c + 2] = o4.z; start[c + 3] = o4.w;
+            } else {
+                for (int k = c; k < c1; k++) {
+                    const int v = count[k];
+                    count[k] = 0;
+                    start[k] = e;
+                    e += v;
+                }
+            }
+        }
+        if (tid == SMALL_BS - 1) start[ncell] = e;           // = total: empty chunks carry it
     }
-    if (tid == 0) start[ncell] = carry;
     __syncthreads();
 
     // 3. members of every cell (arbitrary order), 4. sorted copies (deterministic order)
