@@ -292,7 +292,11 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
                 const float ex = fmaxf(fmaxf(blo[0] - q.x, q.x - bhi[0]), 0.0f);
                 const float ey = fmaxf(fmaxf(blo[1] - q.y, q.y - bhi[1]), 0.0f);
                 const float ez = fmaxf(fmaxf(blo[2] - q.z, q.z - bhi[2]), 0.0f);
+#ifdef GC_NO_CULL
+                const bool keep = v;
+#else
                 const bool keep = v && fmaf(ex, ex, fmaf(ey, ey, ez * ez)) <= cull2;
+#endif
                 const unsigned m = __ballot_sync(0xffffffffu, keep);
                 if (keep) {
                     // explicit shared-space stores: one address, five immediate offsets
