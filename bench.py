@@ -215,6 +215,16 @@ def run_reference_arm(args):
 
 
 def workload_config(design, args, how, reference=False):
+    if reference:
+        return {
+            "workload": "diploid interphase stage (BASELINE configs[0]/[2] topology), ensemble of "
+                        "independent cell trajectories",
+            "beads_per_cell": int(design.n), "chains": int(len(design.chains)),
+            "cells_per_gpu": None, "sim_steps_per_bench_step": args.cpu_sample_steps,
+            "timestep": 1e-5, "contact_map_interval": 20, "start_state": how,
+            "l2": "n/a (host run)",
+            "parallelism": "reference CPU code, one single-threaded trajectory per host core",
+        }
     return {
         "workload": "diploid interphase stage (BASELINE configs[0]/[2] topology), ensemble of "
                     "independent cell trajectories",
