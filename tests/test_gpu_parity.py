@@ -137,6 +137,71 @@ def test_mitotic_forces(oracle_kind):
                                                            abs=1e-6), name
 
 
+def test_full_size_diploid_cell(oracle_kind):
+    """BASELINE.json configs[0] at its FULL size (46 chains, 60,672 beads): pair sets and contact
+    triples bit-exact, forces / energy / wall statistics within 1e-5 against the oracle, plus
+    size-independent properties (Newton's third law for the pair and bonded terms, bit
+    reproducibility, identical replicas from identical seeds)."""
+    cfg = synth.InterphaseConfig()
+    d = synth.make_diploid_design(scale=1.0, cfg=cfg)
+    assert d.n > 60000 and len(d.chains) == 46
+    x = synth.globule_positions(d, seed=1, radius=1.5).astype(np.float32).astype(np.float64)
+    g = gpu(d.n, 2)
+    o = O.OracleSystem(d.n, oracle_kind)
+    for s in (g, o):
+        terms = stages.setup_interphase(s, d, cfg)
+        s.set_positions(x)
+        s.set_context(core_scale=0.5, bond_scale=0.5, semiaxes=(1.6, 1.5, 1.55),
+                      contact_distance=cfg.contactmap_distance * 0.5)
+    # neighbour search: list radius and contact distance
+    for radius in (0.15, 0.12):
+        a, b = g.neighbor_pairs(radius), o.neighbor_pairs(radius)
+        assert len(b) > 5 * d.n
+        np.testing.assert_array_equal(a, b)
+    # forces per term and in total, energy, wall statistics
+    for name, t in terms.items():
+        Fg, Fo = g.compute_force(1 << t), o.compute_force(1 << t)
+        if np.abs(Fo).max() == 0:
+            assert np.abs(Fg).max() == 0, name
+            continue
+        assert rel_force_err(Fg, Fo) < FORCE_TOL, name
+        if name in ("repulsion", "chain", "loops", "nor_bonds", "droplet"):
+            # internal forces cancel: |sum F| << sum |F|
+            assert np.abs(Fg.sum(axis=0)).max() < 2e-6 * np.abs(Fg).sum(), name
+    Fg, Fo = g.compute_force(), o.compute_force()
+    assert rel_force_err(Fg, Fo) < FORCE_TOL
+    assert g.compute_energy() == pytest.approx(o.compute_energy(), rel=2e-5)
+    cg, co = g.get_context(), o.get_context()
+    assert cg.reaction_force == pytest.approx(co.reaction_force, rel=1e-5)
+    # one contact update at the contact distance in force == the pair set at that distance
+    g.contacts_update()
+    o.contacts_update()
+    trip = g.contacts_fetch()
+    np.testing.assert_array_equal(trip, o.contacts_fetch())
+    np.testing.assert_array_equal(trip[:, :2], o.neighbor_pairs(cfg.contactmap_distance * 0.5))
+    assert np.all(trip[:, 2] == 1)
+    g.contacts_clear()
+    # 60 steps (plain launches, then graph replays): both replicas carry the same seed and
+    # must stay bit-identical; a second context reproduces them bit for bit
+    stages.interphase_callback0(g, cfg)
+    g.set_seeds([5, 5])
+    g.run(60, cfg.timestep)
+    x0, x1 = g.get_positions_f32(0), g.get_positions_f32(1)
+    assert np.array_equal(x0, x1)
+    assert np.isfinite(x0).all() and np.abs(x0 - x).max() > 1e-3
+    g.close()
+    h = gpu(d.n, 1)
+    stages.setup_interphase(h, d, cfg)
+    h.set_positions(x)
+    h.set_context(core_scale=0.5, bond_scale=0.5, semiaxes=(1.6, 1.5, 1.55),
+                  contact_distance=cfg.contactmap_distance * 0.5)
+    stages.interphase_callback0(h, cfg)
+    h.set_seeds([5])
+    h.run(60, cfg.timestep)
+    assert np.array_equal(h.get_positions_f32(0), x0)
+    h.close()
+
+
 # ---------------------------------------------------------------------------
 # trajectories under injected noise
 # ---------------------------------------------------------------------------
