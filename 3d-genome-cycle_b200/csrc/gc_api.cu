@@ -91,6 +91,7 @@ struct gc_ctx {
     // the pair kernel of the others instead of leaving the GPU idle.
     int groups = 1;
     int group_grid_x = 1;       // pair-kernel blocks of one group
+    bool dense_pair = false;    // launches being recorded use the 9-blocks-per-SM pair kernel
     std::vector<cudaStream_t> group_streams;
     std::vector<cudaEvent_t> group_events;   // [0] fork, [1 + g] join of group g
 
@@ -235,7 +236,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         // resident blocks per SM of k_pair_cells (60 registers, 26 KB shared memory:
         // __launch_bounds__(128, GC_CELL_MINBLOCKS)); measured best at 8, profiles/r1_notes.md
         int per_sm = GC_CELL_MINBLOCKS;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells<false>, CW * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pair_cells<false, GC_CELL_MINBLOCKS>, CW * 32, 0);
         if (const char *env = getenv("GC_TILE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(env));
         ctx->tile_grid_x = sms * per_sm;        // 1-D: blocks serve all replicas
         ctx->pdl = getenv("GC_NO_PDL") == nullptr;
@@ -854,10 +855,23 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
 // fuse_rebuild (fixed dt, small path): the epilogue also builds the NEXT step's cell list
 void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled, bool fuse_rebuild = false)
 {
+    // (the macro stringifies its kernel argument for the profiler: keep the names short)
+    constexpr auto k_pair_cells_plain = k_pair_cells<true, GC_CELL_MINBLOCKS>;
+    constexpr auto k_pair_cells_ab = k_pair_cells<false, GC_CELL_MINBLOCKS>;
+    constexpr auto k_pair_cells_plain_dense = k_pair_cells<true, MINBLOCKS_DENSE>;
+    constexpr auto k_pair_cells_ab_dense = k_pair_cells<false, MINBLOCKS_DENSE>;
     if (ctx->hp.pair.mode == PAIR_PLAIN) {
-        LAUNCH(ctx, k_pair_cells<true>, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        if (ctx->dense_pair) {
+            LAUNCH(ctx, k_pair_cells_plain_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        } else {
+            LAUNCH(ctx, k_pair_cells_plain, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        }
     } else {
-        LAUNCH(ctx, k_pair_cells<false>, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        if (ctx->dense_pair) {
+            LAUNCH(ctx, k_pair_cells_ab_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        } else {
+            LAUNCH(ctx, k_pair_cells_ab, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+        }
     }
     dim3 gf = bead_grid(ctx, BS);
     const int gr = ctx->n_rep;
@@ -976,6 +990,7 @@ bool ensure_step_graph(gc_ctx *ctx, long long interval)
             ctx->hp = params_window(full, r0, r1 - r0);
             ctx->n_rep = r1 - r0;
             ctx->tile_grid_x = ctx->group_grid_x;
+            ctx->dense_pair = getenv("GC_NO_DENSE_PAIR") == nullptr;
             record_block();
             cudaEventRecord(ctx->group_events[1 + g], ctx->group_streams[g]);
         }
@@ -983,6 +998,7 @@ bool ensure_step_graph(gc_ctx *ctx, long long interval)
         ctx->hp = full;
         ctx->n_rep = R;
         ctx->tile_grid_x = grid_full;
+        ctx->dense_pair = false;
         for (int g = 0; g < G; g++) cudaStreamWaitEvent(main_stream, ctx->group_events[1 + g], 0);
     } else {
         record_block();
@@ -1648,9 +1664,9 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
     if (ctx->hp.pair.mode == PAIR_PLAIN) {
-        LAUNCH(ctx, k_pair_cells<true>, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+        LAUNCH(ctx, (k_pair_cells<true, GC_CELL_MINBLOCKS>), ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
     } else {
-        LAUNCH(ctx, k_pair_cells<false>, ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
+        LAUNCH(ctx, (k_pair_cells<false, GC_CELL_MINBLOCKS>), ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
     }
     const int owned = P.own_hi - P.own_lo;
     LAUNCH(ctx, k_finish<STEP_FUSED>, dim3(std::max((owned + BS - 1) / BS, 1), 1), BS, ctx->hp, 0u, 1);

@@ -74,13 +74,22 @@ __device__ __forceinline__ void pair_accumulate(float xi, float yi, float zi, fl
 // FADD2): the FP32 pipe still retires 128 lanes per clock, but every issued
 // instruction now carries two pair evaluations, which takes the kernel off the
 // issue-slot limit (profiles/r1_notes.md).
-struct CellWarpSmem {
-    float2 tx[CCAP / 2], ty[CCAP / 2], tz[CCAP / 2];
-    float2 tA[CCAP / 2], tB[CCAP / 2];   // pre-scaled mixing factors A', B'
+template<int CAP>
+struct CellWarpSmemT {
+    static_assert(CAP % 2 == 0, "candidates are staged in pairs");
+    float2 tx[CAP / 2], ty[CAP / 2], tz[CAP / 2];
+    float2 tA[CAP / 2], tB[CAP / 2];     // pre-scaled mixing factors A', B'
     int row_off[33];                     // first flattened index of each row (+ sentinel)
     int row_shift[32];                   // slot = flattened index + row_shift[row]
 };
-static_assert(CCAP % 2 == 0, "candidates are staged in pairs");
+using CellWarpSmem = CellWarpSmemT<CCAP>;
+// The pair kernel exists in two shapes: GC_CELL_MINBLOCKS = 8 resident blocks per SM (64
+// registers) for launches that own the GPU, and 9 (56 registers) for the replica-group
+// branches of the step graph, where several pair kernels share the SMs and the extra
+// resident warps pay (+3.7 %, profiles/r1_notes.md).  Both use the same 288-candidate tile
+// (9 blocks x 24 KB fit an SM), hence the same chunking of long candidate lists and the same
+// summation order: a trajectory does not depend on which shape ran a step.
+constexpr int PAIR_CAP = 288, MINBLOCKS_DENSE = 9;
 
 __device__ __forceinline__ float2 neg2(float2 v) { return make_float2(-v.x, -v.y); }
 __device__ __forceinline__ float2 max0(float2 v) { return make_float2(fmaxf(v.x, 0.0f), fmaxf(v.y, 0.0f)); }
@@ -88,7 +97,8 @@ __device__ __forceinline__ float2 max0(float2 v) { return make_float2(fmaxf(v.x,
 // Home-bead pass over the staged tile [0, nt): lanes = H beads x S slices; slice s
 // takes candidate pairs s, s + S, s + 2 S, ... (packed math), then the ragged tail
 // one candidate at a time.
-__device__ __forceinline__ void cell_pass(const CellWarpSmem &sm, int nt, int S, int s,
+template<class SM>
+__device__ __forceinline__ void cell_pass(const SM &sm, int nt, int S, int s,
                                           float4 me, float Ai, float Bi, float kA2, float kB2,
                                           float &fx, float &fy, float &fz)
 {
@@ -143,12 +153,14 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
     }
 }
 
-template<bool PLAIN>
-__global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
+template<bool PLAIN, int MINB>
+__global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
     GC_PDL_ENTRY();
-    __shared__ CellWarpSmem s_warp[CW];
+    constexpr int CAP = PAIR_CAP;
+    using CellSmem = CellWarpSmemT<CAP>;
+    __shared__ CellSmem s_warp[CW];
 
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -166,13 +178,13 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
     const int M = P.cells_per_cut;
     const int side = 2 * M + 1, nrows = side * side;
     constexpr bool plain = PLAIN;          // one soft core, no A/B mixing (mitotic stages)
-    CellWarpSmem &sm = s_warp[warp];
-    // tx, ty, tz, tA, tB are consecutive arrays of CCAP floats (static_assert below)
+    CellSmem &sm = s_warp[warp];
+    // tx, ty, tz, tA, tB are consecutive arrays of CAP floats (static_assert below)
     const unsigned tile_addr = (unsigned) __cvta_generic_to_shared(sm.tx);
-    static_assert(offsetof(CellWarpSmem, ty) == sizeof(float2) * (CCAP / 2) &&
-                  offsetof(CellWarpSmem, tz) == 2 * sizeof(float2) * (CCAP / 2) &&
-                  offsetof(CellWarpSmem, tA) == 3 * sizeof(float2) * (CCAP / 2) &&
-                  offsetof(CellWarpSmem, tB) == 4 * sizeof(float2) * (CCAP / 2), "tile layout");
+    static_assert(offsetof(CellSmem, ty) == sizeof(float2) * (CAP / 2) &&
+                  offsetof(CellSmem, tz) == 2 * sizeof(float2) * (CAP / 2) &&
+                  offsetof(CellSmem, tA) == 3 * sizeof(float2) * (CAP / 2) &&
+                  offsetof(CellSmem, tB) == 4 * sizeof(float2) * (CAP / 2), "tile layout");
 
     // Blocks are not tied to a replica: every warp works through the queues of all
     // replicas round-robin, starting at a different one, so an ensemble is balanced
@@ -301,7 +313,7 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
                 if (keep) {
                     // explicit shared-space stores: one address, five immediate offsets
                     const unsigned a = tile_addr + 4u * (unsigned) (nt + __popc(m & lt_mask));
-                    constexpr unsigned kStride = (unsigned) (sizeof(float2) * (CCAP / 2));
+                    constexpr unsigned kStride = (unsigned) (sizeof(float2) * (CAP / 2));
                     asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(q.x) : "memory");
                     asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + kStride), "f"(q.y) : "memory");
                     asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 2 * kStride), "f"(q.z) : "memory");
@@ -309,7 +321,7 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_pair_cells(const
                     asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 4 * kStride), "f"(plain ? 0.0f : hB * ab.y) : "memory");
                 }
                 nt += __popc(m);
-                if (nt > CCAP - 32 || kin >= total) {          // tile full or input exhausted
+                if (nt > CAP - 32 || kin >= total) {          // tile full or input exhausted
                     __syncwarp();
                     // ---- 3. H home beads x S slices, branch-free -------------------
                     cell_pass(sm, nt, Sa, sa, ma, Aa, Ba, kA2, kB2, fax, fay, faz);
