@@ -14,7 +14,8 @@
 //   2. the warp stages that list into ITS OWN shared-memory tile, coalesced per
 //      row, as (x, y, z, A') + B' with the A/B mixing factors pre-scaled;
 //   3. lanes split into H home beads x S candidate slices (H * S <= 32, chosen per
-//      cell) and evaluate EVERY staged candidate branch-free: the clamped soft
+//      cell; cells with more than 16 beads are served in groups of 16, each with its own
+//      culled tile) and evaluate EVERY staged candidate branch-free: the clamped soft
 //      cores vanish identically beyond their diameter, so there is no distance
 //      test, no ballot and no compaction (packed FP32x2 math, 16.5 issued
 //      instructions per pair);
@@ -45,8 +46,10 @@ constexpr int CCAP = GC_CCAP;            // candidates per tile chunk
 // kRecip[d] = 65536 / d + 1: x / d == (x * kRecip[d]) >> 16 for x * d < 65536 (lane splits,
 // slice counts and tile lengths are all far below); index 0 is unused
 __constant__ unsigned int kRecip[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
-constexpr int CHMAX = 16;                // home beads per pass
-constexpr int CGROUP = 2 * CHMAX;        // home beads per staged tile (two passes)
+// Home beads per staged tile.  (A 32-bead tile evaluated in two 16-bead passes was
+// measured against this: the second pass' live registers cost more than re-staging the
+// few cells with more than 16 beads, and the per-group bounding box culls tighter.)
+constexpr int CHMAX = 16;
 
 // One soft-core pair, branchless (see header).  sA = 0.5 cA (a_i + a_j) and
 // sB = 0.5 cB (b_i + b_j) arrive pre-scaled:
@@ -84,12 +87,18 @@ struct CellWarpSmemT {
 };
 using CellWarpSmem = CellWarpSmemT<CCAP>;
 // The pair kernel exists in two shapes: GC_CELL_MINBLOCKS = 8 resident blocks per SM (64
-// registers) for launches that own the GPU, and 9 (56 registers) for the replica-group
+// registers) for launches that own the GPU, and 10 (48 registers) for the replica-group
 // branches of the step graph, where several pair kernels share the SMs and the extra
-// resident warps pay (+3.7 %, profiles/r1_notes.md).  Both use the same 288-candidate tile
-// (9 blocks x 24 KB fit an SM), hence the same chunking of long candidate lists and the same
+// resident warps pay (profiles/r1_notes.md).  Both use the same 256-candidate tile
+// (10 blocks x 21 KB fit an SM), hence the same chunking of long candidate lists and the same
 // summation order: a trajectory does not depend on which shape ran a step.
-constexpr int PAIR_CAP = 288, MINBLOCKS_DENSE = 9;
+#ifndef GC_PAIR_CAP
+#define GC_PAIR_CAP 256
+#endif
+#ifndef GC_DENSE_MINBLOCKS
+#define GC_DENSE_MINBLOCKS 10
+#endif
+constexpr int PAIR_CAP = GC_PAIR_CAP, MINBLOCKS_DENSE = GC_DENSE_MINBLOCKS;
 
 __device__ __forceinline__ float2 neg2(float2 v) { return make_float2(-v.x, -v.y); }
 __device__ __forceinline__ float2 max0(float2 v) { return make_float2(fmaxf(v.x, 0.0f), fmaxf(v.y, 0.0f)); }
@@ -237,26 +246,19 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
         if (lane == 0) sm.row_off[32] = total;
         __syncwarp();
 
-        for (int g0 = 0; g0 < nhome; g0 += CGROUP) {           // home beads, <= 32 per tile
-            const int ng = min(CGROUP, nhome - g0);
-            // pass a: beads [g0, g0 + Ha), pass b: beads [g0 + Ha, g0 + ng)
-            const int Ha = min(CHMAX, ng), Hb = ng - Ha;
-            const unsigned ra = kRecip[Ha], rb = kRecip[max(Hb, 1)];
-            const int Sa = (int) ((32u * ra) >> 16), Sb = Hb > 0 ? (int) ((32u * rb) >> 16) : 1;
-            const int sa = (int) (((unsigned) lane * ra) >> 16), ha = lane - sa * Ha;
-            const int sb = Hb > 0 ? (int) (((unsigned) lane * rb) >> 16) : 0;
-            const int hb = Hb > 0 ? lane - sb * Hb : 0;
-            const float4 ma = __ldg(&sp[h0 + g0 + ha]);
-            const int ib = Hb > 0 ? g0 + Ha + hb : g0;         // pass b idles on bead g0
-            const float4 mb = __ldg(&sp[h0 + ib]);
-            float Aa = hA, Ba = 0.0f, Ab = hA, Bb = 0.0f;
+        for (int g0 = 0; g0 < nhome; g0 += CHMAX) {            // home beads, <= 16 per tile
+            const int ng = min(CHMAX, nhome - g0);
+            // lanes = ng home beads x S candidate slices
+            const unsigned rh = kRecip[ng];
+            const int S = (int) ((32u * rh) >> 16);
+            const int sl = (int) (((unsigned) lane * rh) >> 16), hl = lane - sl * ng;
+            const float4 me = __ldg(&sp[h0 + g0 + hl]);
+            float Ai = hA, Bi = 0.0f;
             if (!plain) {
-                const float2 aba = __ldg(&sab[h0 + g0 + ha]);
-                const float2 abb = __ldg(&sab[h0 + ib]);
-                Aa = hA * aba.x; Ba = hB * aba.y;
-                Ab = hA * abb.x; Bb = hB * abb.y;
+                const float2 abi = __ldg(&sab[h0 + g0 + hl]);
+                Ai = hA * abi.x; Bi = hB * abi.y;
             }
-            float fax = 0.f, fay = 0.f, faz = 0.f, fbx = 0.f, fby = 0.f, fbz = 0.f;
+            float fx = 0.f, fy = 0.f, fz = 0.f;
 
             // ---- 2. stage: flattened, coalesced within each row, culled, compacted --------
             // The loads of the next 32 candidates are issued before the current 32 are
@@ -324,19 +326,14 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
                 if (nt > CAP - 32 || kin >= total) {          // tile full or input exhausted
                     __syncwarp();
                     // ---- 3. H home beads x S slices, branch-free -------------------
-                    cell_pass(sm, nt, Sa, sa, ma, Aa, Ba, kA2, kB2, fax, fay, faz);
-                    if (Hb > 0) cell_pass(sm, nt, Sb, sb, mb, Ab, Bb, kA2, kB2, fbx, fby, fbz);
+                    cell_pass(sm, nt, S, sl, me, Ai, Bi, kA2, kB2, fx, fy, fz);
                     __syncwarp();                              // tile fully consumed
                     nt = 0;
                 }
             }
             // ---- 4. fold the slices, store -----------------------------------------
-            cell_fold(Ha, Sa, lane, fax, fay, faz);
-            if (lane < Ha) pforce[h0 + g0 + lane] = make_float4(fax, fay, faz, 0.0f);
-            if (Hb > 0) {
-                cell_fold(Hb, Sb, lane, fbx, fby, fbz);
-                if (lane < Hb) pforce[h0 + g0 + Ha + lane] = make_float4(fbx, fby, fbz, 0.0f);
-            }
+            cell_fold(ng, S, lane, fx, fy, fz);
+            if (lane < ng) pforce[h0 + g0 + lane] = make_float4(fx, fy, fz, 0.0f);
         }
     }
     }   // replicas
