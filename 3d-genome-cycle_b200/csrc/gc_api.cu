@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <utility>
 #include <vector>
 
@@ -69,6 +70,10 @@ struct gc_ctx {
     unsigned long long *d_counter = nullptr;
     void *d_scratch = nullptr;
     size_t scratch_cap = 0;
+    // parked temporary buffers (dev_alloc / dev_free)
+    std::vector<std::pair<void *, size_t>> cache;
+    size_t cache_bytes = 0;
+    std::unordered_map<void *, size_t> alloc_bytes;
 
     long long run_step = 0;     // host mirror of RepState::step
     int parity = 0;             // host mirror of RepState::parity (replicas move in lockstep)
@@ -142,14 +147,36 @@ int fail(gc_ctx *ctx, int code, const char *fmt, ...)
             return fail(ctx, GC_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e_));       \
     } while (0)
 
+// Temporary device buffers (contact reduction, frames, queries) come and go at output
+// cadence; cudaMalloc / cudaFree synchronise the device and were seen to stall for hundreds
+// of milliseconds, so released blocks of >= 256 KiB are parked in the context (at most 16
+// blocks / 8 GiB) and handed out again to requests of at least half their size.
+constexpr size_t CACHE_MIN_BYTES = 256u << 10, CACHE_MAX_BLOCKS = 16;
+constexpr size_t CACHE_MAX_BYTES = (size_t) 8 << 30;
+
 template<typename T>
 int dev_alloc(gc_ctx *ctx, T **out, size_t count, int fill_byte = 0)
 {
     void *p = nullptr;
     size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
-    GC_CUDA(ctx, cudaMalloc(&p, bytes));
+    int best = -1;
+    for (int k = 0; k < (int) ctx->cache.size(); k++) {
+        const size_t have = ctx->cache[k].second;
+        if (have >= bytes && have <= 2 * bytes &&
+            (best < 0 || have < ctx->cache[best].second)) {
+            best = k;
+        }
+    }
+    if (best >= 0) {
+        p = ctx->cache[best].first;
+        ctx->cache_bytes -= ctx->cache[best].second;
+        ctx->cache.erase(ctx->cache.begin() + best);          // still listed in ctx->allocs
+    } else {
+        GC_CUDA(ctx, cudaMalloc(&p, bytes));
+        ctx->allocs.push_back(p);
+        ctx->alloc_bytes[p] = bytes;
+    }
     GC_CUDA(ctx, cudaMemsetAsync(p, fill_byte, bytes, ctx->stream));
-    ctx->allocs.push_back(p);
     *out = (T *) p;
     return GC_OK;
 }
@@ -157,8 +184,19 @@ int dev_alloc(gc_ctx *ctx, T **out, size_t count, int fill_byte = 0)
 void dev_free(gc_ctx *ctx, void *p)
 {
     if (!p) return;
+    auto sz = ctx->alloc_bytes.find(p);
+    const size_t bytes = sz != ctx->alloc_bytes.end() ? sz->second : 0;
+    if (bytes >= CACHE_MIN_BYTES && ctx->cache.size() < CACHE_MAX_BLOCKS &&
+        ctx->cache_bytes + bytes <= CACHE_MAX_BYTES) {
+        // later work on the stream may still read it: order the reuse after it
+        cudaStreamSynchronize(ctx->stream);
+        ctx->cache.emplace_back(p, bytes);
+        ctx->cache_bytes += bytes;
+        return;
+    }
     auto it = std::find(ctx->allocs.begin(), ctx->allocs.end(), p);
     if (it != ctx->allocs.end()) ctx->allocs.erase(it);
+    if (sz != ctx->alloc_bytes.end()) ctx->alloc_bytes.erase(sz);
     cudaFree(p);
 }
 
