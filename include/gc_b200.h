@@ -12,7 +12,9 @@
  *     available from gc_last_error().  Nothing throws across this boundary.
  *     (The reference signals errors with C++ exceptions)
  *   - one gc_ctx = one CUDA device + one stream + R replicas that share bead
- *     attributes and topology and differ in positions / seed / context.
+ *     attributes and topology and differ in positions / seed / context.  All work is
+ *     ordered on that stream (gc_stream); with R > 1 the replayed step graph forks
+ *     internally into replica-group branches and joins before the launch returns to it.
  *   - term-adding functions return a term id >= 0 usable with
  *     gc_set_term_enabled() and as bit (1u << id) in force/energy masks.
  */
