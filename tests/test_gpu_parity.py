@@ -450,8 +450,9 @@ def test_small_system_path_is_bit_identical_to_the_four_kernel_rebuild(replicas)
         assert np.array_equal(a, b)
 
 
-@pytest.mark.parametrize("scale,replicas", [(0.02, 5), (0.1, 3), (0.1, 11)])
-def test_replica_groups_of_the_step_graph_change_nothing(scale, replicas):
+@pytest.mark.parametrize("scale,replicas,skin", [(0.02, 5, 0.0), (0.1, 3, 0.0), (0.1, 11, 0.0),
+                                                 (0.05, 4, 0.25)])
+def test_replica_groups_of_the_step_graph_change_nothing(scale, replicas, skin):
     """The step graph runs the replicas as parallel branches (one capture stream per group,
     kernel arguments windowed to the group's replicas).  GC_GROUPS=1 is the single-branch
     graph: positions, contact triples and wall state must be bit-identical."""
@@ -461,6 +462,7 @@ def test_replica_groups_of_the_step_graph_change_nothing(scale, replicas):
         g = gpu(d.n, replicas)
         stages.setup_interphase(g, d, cfg)
         g.set_positions(x)
+        g.set_skin(skin)                  # > 0: cells reused while displacements allow
         g.set_seeds(np.arange(11, 11 + replicas, dtype=np.uint64))
         stages.interphase_callback0(g, cfg)
         g.run(150, cfg.timestep)
