@@ -449,8 +449,8 @@ def run_b200_arm(args):
                            f"scalar {fp32_scalar:.2f} and packed {fp32_packed:.2f} TFLOP/s",
             # dram__bytes_read.sum + dram__bytes_write.sum of one k_pair_cells launch from the
             # committed ncu --set full capture of this workload (8 cells, relaxed state)
-            "traffic": 13.53e6 if (R == 8 and args.scale == 1.0 and name.startswith("k_pair_cells")) else None,
-            "traffic_source": "profiles/r1_pair_cells_v6_sparse_ncu_summary.txt (13.50 MB read, 37 KB written "
+            "traffic": 13.12e6 if (R == 8 and args.scale == 1.0 and name.startswith("k_pair_cells")) else None,
+            "traffic_source": "profiles/r1_pair_cells_v8_sparse_ncu_summary.txt (13.12 MB read, 0.5 KB written "
                               "per launch of all 8 cells; algorithmic 32 B x R x N = %.2f MB)" % (32 * R * n / 1e6),
             "timing_note": "kernel_ms_per_launch / kernel_share_of_step come from a serialised pass (plain "
                            "launches, all cells in one launch, CUDA events on the library's stream); the timed "
