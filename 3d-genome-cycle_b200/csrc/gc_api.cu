@@ -286,6 +286,7 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         if (const char *env = getenv("GC_GROUP_BLOCKS_PER_SM")) per_group = std::max(1, atoi(env));
         ctx->groups = std::max(groups, 1);
         ctx->group_grid_x = ctx->groups > 1 ? sms * per_group : ctx->tile_grid_x;
+        if (const char *env = getenv("GC_GROUP_GRID")) ctx->group_grid_x = std::max(1, atoi(env));
         ctx->small = n_beads <= SMALL_MAX_BEADS && P.ncell_max <= SMALL_MAX_CELLS &&
                      getenv("GC_NO_SMALL") == nullptr;
     }
