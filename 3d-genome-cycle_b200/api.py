@@ -72,6 +72,14 @@ SYMBOLS = [
     ("gc_set_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
     ("gc_get_positions_f32", C.c_int, [_P, C.c_int32, C.POINTER(C.c_float)]),
     ("gc_get_frame", C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
+    ("gc_set_positions_all_f32", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_get_positions_all_f32", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_host_alloc", C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    ("gc_host_free", C.c_int, [C.c_void_p]),
+    ("gc_frame_begin", C.c_int, [_P, C.c_int32, C.c_int32]),
+    ("gc_frame_end", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_get_contexts", C.c_int, [_P, C.POINTER(Context)]),
+    ("gc_compute_energy_all", C.c_int, [_P, C.c_uint32, _dp]),
     ("gc_set_seeds", C.c_int, [_P, C.POINTER(C.c_uint64)]),
     ("gc_add_pair_softcore_ab", C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32]),
     ("gc_add_pair_softcore", C.c_int, [_P, C.c_double, C.c_double]),
@@ -191,6 +199,9 @@ class System:
         if getattr(self, "_h", None):
             self.lib.gc_destroy(self._h)
             self._h = None
+            for ptr in getattr(self, "_host_allocs", []):
+                self.lib.gc_host_free(ptr)
+            self._host_allocs = []
 
     def __del__(self):
         try:
@@ -236,6 +247,54 @@ class System:
         out = np.empty((nrep, self.n, 3), dtype=np.float32)
         self._ck(self.lib.gc_get_frame(self._h, int(replica), int(fraction_bits), _ptr(out, C.c_float)))
         return out if replica < 0 else out[0]
+
+    # ---- whole-ensemble transfers (one copy per direction) ---------------------
+    def host_buffer(self, shape=None):
+        """Page-locked float32 array (default [R, n, 3]) for the *_all transfers; it is
+        freed with the System."""
+        shape = tuple(shape) if shape is not None else (self.n_rep, self.n, 3)
+        count = int(np.prod(shape))
+        ptr = C.c_void_p()
+        if self.lib.gc_host_alloc(count * 4, C.byref(ptr)) != 0:
+            raise GcError(-2, "gc_host_alloc failed")
+        self._host_allocs = getattr(self, "_host_allocs", [])
+        self._host_allocs.append(ptr)
+        buf = (C.c_float * count).from_address(ptr.value)
+        return np.frombuffer(buf, dtype=np.float32).reshape(shape)
+
+    def set_positions_all_f32(self, xyz):
+        x = xyz if (isinstance(xyz, np.ndarray) and xyz.dtype == np.float32 and
+                    xyz.flags.c_contiguous) else np.ascontiguousarray(xyz, dtype=np.float32)
+        assert x.size == self.n_rep * self.n * 3
+        self._ck(self.lib.gc_set_positions_all_f32(self._h, _ptr(x, C.c_float)))
+        self._keep_upload = x            # a page-locked source is read asynchronously
+
+    def get_positions_all_f32(self, out=None):
+        if out is None:
+            out = np.empty((self.n_rep, self.n, 3), dtype=np.float32)
+        assert out.dtype == np.float32 and out.flags.c_contiguous and out.size == self.n_rep * self.n * 3
+        self._ck(self.lib.gc_get_positions_all_f32(self._h, _ptr(out, C.c_float)))
+        return out
+
+    def frame_begin(self, replica=-1, fraction_bits=16):
+        """Starts an asynchronous quantised frame; steps queued afterwards overlap its copy."""
+        self._frame_shape = (self.n_rep if replica < 0 else 1, self.n, 3)
+        self._ck(self.lib.gc_frame_begin(self._h, int(replica), int(fraction_bits)))
+
+    def frame_end(self):
+        out = np.empty(self._frame_shape, dtype=np.float32)
+        self._ck(self.lib.gc_frame_end(self._h, _ptr(out, C.c_float)))
+        return out
+
+    def get_contexts(self):
+        arr = (Context * self.n_rep)()
+        self._ck(self.lib.gc_get_contexts(self._h, arr))
+        return list(arr)
+
+    def compute_energy_all(self, mask=GC_MASK_ALL):
+        e = np.empty(self.n_rep, dtype=np.float64)
+        self._ck(self.lib.gc_compute_energy_all(self._h, mask, _ptr(e, C.c_double)))
+        return e
 
     def set_seeds(self, seeds):
         s = np.ascontiguousarray(seeds, dtype=np.uint64)

@@ -64,6 +64,14 @@ struct gc_ctx {
     int *d_well_targets = nullptr;
     float *d_frame = nullptr;   // gc_get_frame staging
     size_t frame_cap = 0;
+    // whole-ensemble host transfers (gc_*_positions_all_f32, gc_frame_begin / _end): one
+    // page-locked host buffer + one device buffer of packed f32, a copy stream and an event
+    float *h_stage = nullptr, *d_stage = nullptr;
+    size_t stage_cap = 0;
+    float *h_frame = nullptr;
+    size_t h_frame_cap = 0, frame_pending = 0;   // floats of the frame in flight (0 = none)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_event = nullptr;
     float *d_noise = nullptr;
     size_t noise_cap = 0;
     double *d_partials = nullptr;
@@ -347,6 +355,10 @@ int gc_destroy(gc_ctx *ctx)
         for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
     }
     for (void *p : ctx->allocs) cudaFree(p);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->copy_event) cudaEventDestroy(ctx->copy_event);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    if (ctx->h_frame) cudaFreeHost(ctx->h_frame);
     if (ctx->step_graph) cudaGraphExecDestroy(ctx->step_graph);
     for (cudaStream_t gs : ctx->group_streams) cudaStreamDestroy(gs);
     for (cudaEvent_t ge : ctx->group_events) cudaEventDestroy(ge);
@@ -463,7 +475,7 @@ int gc_set_seeds(gc_ctx *ctx, const uint64_t *seeds)
 {
     GC_CHECK_CTX(ctx);
     if (!seeds) return fail(ctx, GC_ERR_INVALID, "seeds is null");
-    return modify_states(ctx, -1, [&](RepState &st, int r) { st.seed = seeds[r]; });
+    return modify_states(ctx, -1, [&](RepState &st, int r) { st.seed = seeds[r]; st.epoch = 0; });
 }
 
 // ---------------------------------------------------------------------------
@@ -668,6 +680,33 @@ int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out)
     for (int k = 0; k < 3; k++) {
         out->semiaxes[k] = st.semiaxes[k];
         out->axial_reaction[k] = st.axial[k];
+    }
+    return GC_OK;
+}
+
+int gc_get_contexts(gc_ctx *ctx, gc_context *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out) return fail(ctx, GC_ERR_INVALID, "bad args");
+    std::vector<RepState> st((size_t) ctx->n_rep);
+    GC_CUDA(ctx, cudaMemcpyAsync(st.data(), ctx->hp.st, st.size() * sizeof(RepState),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < ctx->n_rep; r++) {
+        gc_context &o = out[r];
+        const RepState &s = st[r];
+        o.time = s.time;
+        o.core_scale = s.core_scale;
+        o.bond_scale = s.bond_scale;
+        o.contact_distance = s.contact_distance;
+        o.reaction_force = s.reaction;
+        o.last_timestep = s.dt_last;
+        o.step = s.step;
+        o.rebuilds = s.rebuilds;
+        for (int k = 0; k < 3; k++) {
+            o.semiaxes[k] = s.semiaxes[k];
+            o.axial_reaction[k] = s.axial[k];
+        }
     }
     return GC_OK;
 }
@@ -888,6 +927,7 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
     st.step = 0;
     st.dt_last = dt;
     st.dt_prev = dt;
+    st.epoch += 1;        // a new logical run draws a new noise stream
 }
 
 // one force evaluation (+ update when fused) for every replica
@@ -1173,6 +1213,7 @@ int gc_get_frame(gc_ctx *ctx, int32_t replica, int32_t fraction_bits, float *xyz
     if (!xyz || replica < -1 || replica >= ctx->n_rep || fraction_bits < 1 || fraction_bits > 24) {
         return fail(ctx, GC_ERR_INVALID, "bad args");
     }
+    if (ctx->frame_pending) return fail(ctx, GC_ERR_STATE, "a frame is in flight (gc_frame_end first)");
     const int r0 = replica < 0 ? 0 : replica, nrep = replica < 0 ? ctx->n_rep : 1;
     const size_t count = (size_t) nrep * ctx->n * 3;
     if (count == 0) return GC_OK;
@@ -1189,6 +1230,154 @@ int gc_get_frame(gc_ctx *ctx, int32_t replica, int32_t fraction_bits, float *xyz
     GC_CUDA(ctx, cudaMemcpyAsync(xyz, ctx->d_frame, count * sizeof(float), cudaMemcpyDeviceToHost,
                                  ctx->stream));
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// page-locked host + device staging of `floats` packed f32, copy stream, event
+int ensure_stage(gc_ctx *ctx, size_t floats)
+{
+    if (!ctx->copy_stream) {
+        GC_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        GC_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming));
+    }
+    if (floats <= ctx->stage_cap) return GC_OK;
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    if (ctx->d_stage) dev_free(ctx, ctx->d_stage);
+    ctx->h_stage = nullptr;
+    ctx->d_stage = nullptr;
+    ctx->stage_cap = 0;
+    GC_CUDA(ctx, cudaMallocHost(&ctx->h_stage, floats * sizeof(float)));
+    int rc = dev_alloc(ctx, &ctx->d_stage, floats);
+    if (rc) return rc;
+    ctx->stage_cap = floats;
+    return GC_OK;
+}
+
+// true when `p` is page-locked host memory (then copies need no staging pass)
+bool is_pinned(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int ensemble_blocks(const gc_ctx *ctx)
+{
+    const size_t total = (size_t) ctx->n_rep * ctx->n;
+    return (int) std::max<size_t>(1, std::min<size_t>((total + 255) / 256, 148 * 8));
+}
+
+} // namespace
+
+extern "C" {
+
+int gc_set_positions_all_f32(gc_ctx *ctx, const float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz) return fail(ctx, GC_ERR_INVALID, "bad args");
+    const size_t floats = (size_t) ctx->n_rep * ctx->n * 3;
+    if (floats == 0) return GC_OK;
+    int rc = ensure_stage(ctx, floats);
+    if (rc) return rc;
+    const float *src = xyz;
+    if (!is_pinned(xyz)) {
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));      // the staging buffer is free again
+        memcpy(ctx->h_stage, xyz, floats * sizeof(float));
+        src = ctx->h_stage;
+    }
+    GC_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage, src, floats * sizeof(float), cudaMemcpyHostToDevice,
+                                 ctx->stream));
+    LAUNCH(ctx, k_unpack_positions, ensemble_blocks(ctx), 256, ctx->hp, (const float *) ctx->d_stage);
+    // asynchronous: later work of this context is ordered behind it on the stream; a
+    // pinned caller buffer must stay untouched until the next synchronising call
+    return GC_OK;
+}
+
+int gc_get_positions_all_f32(gc_ctx *ctx, float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz) return fail(ctx, GC_ERR_INVALID, "bad args");
+    const size_t floats = (size_t) ctx->n_rep * ctx->n * 3;
+    if (floats == 0) return GC_OK;
+    int rc = ensure_stage(ctx, floats);
+    if (rc) return rc;
+    LAUNCH(ctx, k_pack_positions, ensemble_blocks(ctx), 256, ctx->hp, ctx->d_stage);
+    const bool direct = is_pinned(xyz);
+    GC_CUDA(ctx, cudaMemcpyAsync(direct ? xyz : ctx->h_stage, ctx->d_stage, floats * sizeof(float),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!direct) memcpy(xyz, ctx->h_stage, floats * sizeof(float));
+    return GC_OK;
+}
+
+int gc_host_alloc(size_t bytes, void **out)
+{
+    if (!out) return GC_ERR_INVALID;
+    *out = nullptr;
+    return cudaMallocHost(out, std::max<size_t>(bytes, 1)) == cudaSuccess ? GC_OK : GC_ERR_CUDA;
+}
+
+int gc_host_free(void *p)
+{
+    if (!p) return GC_OK;
+    return cudaFreeHost(p) == cudaSuccess ? GC_OK : GC_ERR_CUDA;
+}
+
+int gc_frame_begin(gc_ctx *ctx, int32_t replica, int32_t fraction_bits)
+{
+    GC_CHECK_CTX(ctx);
+    if (replica < -1 || replica >= ctx->n_rep || fraction_bits < 1 || fraction_bits > 24) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    if (ctx->frame_pending) return fail(ctx, GC_ERR_STATE, "a frame is already in flight");
+    const int r0 = replica < 0 ? 0 : replica, nrep = replica < 0 ? ctx->n_rep : 1;
+    const size_t count = (size_t) nrep * ctx->n * 3;
+    if (count == 0) return GC_OK;
+    int rc = ensure_stage(ctx, 1);                               // copy stream + event
+    if (rc) return rc;
+    if (count > ctx->frame_cap) {
+        if (ctx->d_frame) dev_free(ctx, ctx->d_frame);
+        ctx->d_frame = nullptr;
+        ctx->frame_cap = 0;
+        rc = dev_alloc(ctx, &ctx->d_frame, count);
+        if (rc) return rc;
+        ctx->frame_cap = count;
+    }
+    if (count > ctx->h_frame_cap) {
+        if (ctx->h_frame) cudaFreeHost(ctx->h_frame);
+        ctx->h_frame = nullptr;
+        ctx->h_frame_cap = 0;
+        GC_CUDA(ctx, cudaMallocHost(&ctx->h_frame, count * sizeof(float)));
+        ctx->h_frame_cap = count;
+    }
+    const int blocks = (int) std::min<size_t>((count / 3 + 255) / 256, 148 * 8);
+    LAUNCH(ctx, k_frame, std::max(blocks, 1), 256, ctx->hp, r0, nrep, (int) fraction_bits, ctx->d_frame);
+    // the copy leaves on its own stream: steps queued on the launch stream after this call
+    // (they never touch d_frame) overlap the device-to-host transfer
+    GC_CUDA(ctx, cudaEventRecord(ctx->copy_event, ctx->stream));
+    GC_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_event, 0));
+    GC_CUDA(ctx, cudaMemcpyAsync(ctx->h_frame, ctx->d_frame, count * sizeof(float),
+                                 cudaMemcpyDeviceToHost, ctx->copy_stream));
+    ctx->frame_pending = count;
+    return GC_OK;
+}
+
+int gc_frame_end(gc_ctx *ctx, float *xyz)
+{
+    GC_CHECK_CTX(ctx);
+    if (!xyz) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (!ctx->frame_pending) return fail(ctx, GC_ERR_STATE, "no frame in flight");
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    memcpy(xyz, ctx->h_frame, ctx->frame_pending * sizeof(float));
+    ctx->frame_pending = 0;
     return GC_OK;
 }
 
@@ -1250,6 +1439,35 @@ int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *
     double e = 0;
     for (int b = 0; b < nb; b++) e += part[b];
     *out = e;
+    return GC_OK;
+}
+
+int gc_compute_energy_all(gc_ctx *ctx, uint32_t term_mask, double *out)
+{
+    GC_CHECK_CTX(ctx);
+    if (!out) return fail(ctx, GC_ERR_INVALID, "bad args");
+    int rc = finalize(ctx);
+    if (rc) return rc;
+    plan_and_rebuild(ctx, 0.0);
+    launch_rebuild(ctx);
+    const int nb = std::max((ctx->n + BS - 1) / BS, 1), R = ctx->n_rep;
+    double *d_part = nullptr;
+    rc = dev_alloc(ctx, &d_part, (size_t) R * nb);
+    if (rc) return rc;
+    for (int r = 0; r < R; r++) {
+        LAUNCH(ctx, k_energy, nb, BS, ctx->hp, r, term_mask, d_part + (size_t) r * nb);
+    }
+    std::vector<double> part((size_t) R * nb);
+    GC_CUDA(ctx, cudaMemcpyAsync(part.data(), d_part, part.size() * sizeof(double),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    rc = check_device_errors(ctx);
+    dev_free(ctx, d_part);
+    if (rc) return rc;
+    for (int r = 0; r < R; r++) {
+        double e = 0;
+        for (int b = 0; b < nb; b++) e += part[(size_t) r * nb + b];   // block order: deterministic
+        out[r] = e;
+    }
     return GC_OK;
 }
 

@@ -95,7 +95,9 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
         }
     }
     if (!(rlist > 0.0)) rlist = 1.0;
-    double cs = rlist / P.cells_per_cut;
+    // a hair above rlist / M: the FP32 image of the edge (inv_cell) may round the other
+    // way, and M cells must span at least rlist for every pair at exactly that distance
+    double cs = rlist * (1.0 + 1.0e-6) / P.cells_per_cut;
     int dims[3];
     for (;;) {
         double tot = 1.0;

@@ -170,10 +170,14 @@ __device__ __host__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1,
 
 // Three standard normals for (bead, step) of a replica: Box-Muller on the four
 // Philox words.  u in (0, 1): 24 random bits + half-ulp offset.
-__device__ __forceinline__ f3 normal3(unsigned long long seed, uint32_t bead, long long step)
+// `epoch` (counter word 3) counts the logical runs of a context: every restart of gc_run
+// draws a fresh stream, as the reference's drivers seed every simulate_* call with the
+// next output of their mt19937_64 (SIM/stage_interphase/simulation_driver_interphase.cpp:61).
+__device__ __forceinline__ f3 normal3(unsigned long long seed, uint32_t bead, long long step,
+                                      uint32_t epoch)
 {
     uint32_t w[4];
-    philox4x32_10(bead, (uint32_t) step, (uint32_t) ((unsigned long long) step >> 32), 0u,
+    philox4x32_10(bead, (uint32_t) step, (uint32_t) ((unsigned long long) step >> 32), epoch,
                   (uint32_t) seed, (uint32_t) (seed >> 32), w);
     const float S = 1.0f / 16777216.0f;
     float u0 = ((float) (w[0] >> 8) + 0.5f) * S;

@@ -303,7 +303,7 @@ __global__ void k_debug_noise(const __grid_constant__ Params P, int r, long long
     GC_PDL_ENTRY();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
-    f3 z = normal3(P.st[r].seed, (uint32_t) i, step);
+    f3 z = normal3(P.st[r].seed, (uint32_t) i, step, (uint32_t) P.st[r].epoch);
     out[3 * i] = z.x;
     out[3 * i + 1] = z.y;
     out[3 * i + 2] = z.z;
@@ -362,6 +362,34 @@ __global__ void __launch_bounds__(256) k_frame(const __grid_constant__ Params P,
         out[3 * t] = quantize_coord(p.x, bits);
         out[3 * t + 1] = quantize_coord(p.y, bits);
         out[3 * t + 2] = quantize_coord(p.z, bits);
+    }
+}
+
+// Host transfers of whole ensembles (gc_set/get_positions_all_f32): the packed
+// [R][n][3] f32 image of view_positions() is repacked to / from the float4 device
+// layout here, so that each direction is ONE asynchronous copy.
+__global__ void __launch_bounds__(256) k_unpack_positions(const __grid_constant__ Params P,
+                                                          const float *__restrict__ in)
+{
+    GC_PDL_ENTRY();
+    const size_t total = (size_t) P.n_rep * P.n;
+    for (size_t t = (size_t) blockIdx.x * 256 + threadIdx.x; t < total; t += (size_t) gridDim.x * 256) {
+        const int r = (int) (t / P.n);
+        P.pos[P.st[r].parity][t] = make_float4(in[3 * t], in[3 * t + 1], in[3 * t + 2], 0.0f);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pack_positions(const __grid_constant__ Params P,
+                                                        float *__restrict__ out)
+{
+    GC_PDL_ENTRY();
+    const size_t total = (size_t) P.n_rep * P.n;
+    for (size_t t = (size_t) blockIdx.x * 256 + threadIdx.x; t < total; t += (size_t) gridDim.x * 256) {
+        const int r = (int) (t / P.n);
+        const float4 p = P.pos[P.st[r].parity][t];
+        out[3 * t] = p.x;
+        out[3 * t + 1] = p.y;
+        out[3 * t + 2] = p.z;
     }
 }
 

@@ -423,7 +423,7 @@ __device__ __forceinline__ f3 bead_noise(const Params &P, const RepState &st, in
                                         P.n + idx) * 3;
         return {z[0], z[1], z[2]};
     }
-    return normal3(st.seed, (uint32_t) idx, n);
+    return normal3(st.seed, (uint32_t) idx, n, (uint32_t) st.epoch);
 }
 
 __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &st, int r, int t,

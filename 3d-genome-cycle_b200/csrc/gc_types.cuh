@@ -166,7 +166,7 @@ struct RepState {
     int error;                     // sticky: 1 = NaN/Inf seen
     int n_light_cells;             // lightly populated cells, queued from the BACK of cell_list
     int contact_cursor;            // work-queue head of k_contact_cells
-    int pad2;
+    int epoch;                     // logical runs since the seeds were set (Philox counter word 3)
     StepConst sc;
 };
 

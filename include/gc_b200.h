@@ -156,11 +156,29 @@ int gc_set_positions(gc_ctx *ctx, int32_t replica, const double *xyz);
 int gc_get_positions(gc_ctx *ctx, int32_t replica, double *xyz);
 int gc_set_positions_f32(gc_ctx *ctx, int32_t replica, const float *xyz);
 int gc_get_positions_f32(gc_ctx *ctx, int32_t replica, float *xyz);
+/* The same for the whole ensemble in one call: xyz = [R][n_beads][3] f32.  One
+   asynchronous copy per direction (the float3 <-> float4 repack runs on the device).
+   Buffers from gc_host_alloc (page-locked) are transferred in place; any other host
+   pointer goes through the context's page-locked staging buffer.  set returns once the
+   copy is queued (a page-locked source must stay untouched until the next synchronising
+   call, e.g. gc_run); get returns when xyz is filled. */
+int gc_set_positions_all_f32(gc_ctx *ctx, const float *xyz);
+int gc_get_positions_all_f32(gc_ctx *ctx, float *xyz);
+/* Page-locked host memory for the transfers above (cudaMallocHost / cudaFreeHost). */
+int gc_host_alloc(size_t bytes, void **out);
+int gc_host_free(void *p);
 /* Trajectory frame as simulation_store::save_positions stores it
    (SIM/common/simulation_store.cpp:22-32,192-216): every coordinate rounded to
    fraction_bits significant binary digits (16 in the reference) on the device and
    returned as packed f32 [n][3]; replica = -1 returns all replicas, [R][n][3]. */
 int gc_get_frame(gc_ctx *ctx, int32_t replica, int32_t fraction_bits, float *xyz);
+/* The same frame WITHOUT stalling the step loop (the reference writes frames
+   synchronously, SIM/common/simulation_store.cpp:192-216): gc_frame_begin quantises on
+   the launch stream and starts the device-to-host copy on a second stream into a
+   page-locked buffer; steps queued afterwards overlap it.  gc_frame_end waits for that
+   copy only and hands the frame out.  One frame in flight per context. */
+int gc_frame_begin(gc_ctx *ctx, int32_t replica, int32_t fraction_bits);
+int gc_frame_end(gc_ctx *ctx, float *xyz);
 /* Philox key per replica (the drivers draw it from mt19937_64(design.seed),
    SIM/stage_interphase/simulation_driver_interphase.cpp:61). */
 int gc_set_seeds(gc_ctx *ctx, const uint64_t *seeds);
@@ -207,6 +225,9 @@ int gc_set_schedule(gc_ctx *ctx, const gc_schedule *schedule);
 int gc_set_context(gc_ctx *ctx, int32_t replica, const gc_context *in);
 int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out);
 
+/* Contexts of all replicas in one copy: out = [R]. */
+int gc_get_contexts(gc_ctx *ctx, gc_context *out);
+
 /* ---- dynamics ---------------------------------------------------------- */
 
 /* md::simulate_brownian_dynamics incl. the per-step driver callback body
@@ -223,6 +244,11 @@ int gc_debug_noise(gc_ctx *ctx, int32_t replica, int64_t step, float *out);
 int gc_compute_force(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out);
 /* md::system::compute_potential_energy (MD/system.hpp:249-252). */
 int gc_compute_energy(gc_ctx *ctx, int32_t replica, uint32_t term_mask, double *out);
+
+/* The same for every replica with ONE cell-list rebuild and one copy: out = [R]
+   (the drivers log the energy of every cell at sampling cadence,
+   SIM/stage_interphase/simulation_driver_interphase.cpp:24-27). */
+int gc_compute_energy_all(gc_ctx *ctx, uint32_t term_mask, double *out);
 
 /* md::neighbor_searcher<open_box>(box, radius).set_points().search()
    (MD/misc/neighbor_searcher.hpp:22-131): unique pairs i < j with

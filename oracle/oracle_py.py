@@ -24,6 +24,8 @@ LIBS = {
     "reference": ORACLE_DIR / "_ref" / "libgc_ref.so",
     "strict": ORACLE_DIR / "_ref" / "libgc_ref_strict.so",
     "port": ORACLE_DIR / "libgc_port.so",
+    # the reference's literal -march=native build (timed CPU baseline only; see Makefile)
+    "native": ORACLE_DIR / "_ref" / "libgc_ref_native.so",
 }
 
 
@@ -56,7 +58,7 @@ def build(kinds=("port", "reference", "strict"), quiet=True):
         if k == "port":
             targets.append("port")
         elif Path("/root/reference").exists():
-            targets.append("ref" if k == "reference" else "ref_strict")
+            targets.append({"reference": "ref", "strict": "ref_strict", "native": "ref_native"}[k])
     if targets:
         subprocess.run(["make", "-C", str(ORACLE_DIR)] + targets, check=True,
                        stdout=subprocess.DEVNULL if quiet else None)
@@ -67,6 +69,28 @@ _cache = {}
 
 def available(kind):
     return LIBS[kind].exists()
+
+
+def native_usable():
+    """True when the -march=native build exists and this host has every ISA flag of the
+    host it was built on (so it cannot fault on an unsupported instruction)."""
+    lib = LIBS["native"]
+    flags = lib.with_suffix(".flags")
+    if not (lib.exists() and flags.exists()):
+        return False
+    need = set(flags.read_text().split())
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                return need <= set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return False
+
+
+def native_arch():
+    f = LIBS["native"].with_suffix(".arch")
+    return f.read_text().strip() if f.exists() else "unknown"
 
 
 def load(kind="reference"):
