@@ -79,6 +79,7 @@ SYMBOLS = [
     ("gc_frame_begin", C.c_int, [_P, C.c_int32, C.c_int32]),
     ("gc_frame_end", C.c_int, [_P, C.POINTER(C.c_float)]),
     ("gc_get_contexts", C.c_int, [_P, C.POINTER(Context)]),
+    ("gc_set_step", C.c_int, [_P, C.c_int32, C.c_int64]),
     ("gc_compute_energy_all", C.c_int, [_P, C.c_uint32, _dp]),
     ("gc_set_seeds", C.c_int, [_P, C.POINTER(C.c_uint64)]),
     ("gc_add_pair_softcore_ab", C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32]),
@@ -363,6 +364,10 @@ class System:
             else:
                 setattr(c, k, v)
         self._ck(self.lib.gc_set_context(self._h, replica, C.byref(c)))
+
+    def set_step(self, step, replica=-1):
+        """Resume a logical run at `step` (use with run(..., restart=False))."""
+        self._ck(self.lib.gc_set_step(self._h, int(replica), int(step)))
 
     def set_skin(self, frac):
         self._ck(self.lib.gc_set_skin(self._h, float(frac)))

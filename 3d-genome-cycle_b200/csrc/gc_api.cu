@@ -274,8 +274,9 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
         want = (want + 3) & ~3LL;                // k_scan reads the counts as int4
         P.ncell_max = (int) want;
     }
+    // cell edge = list radius.  (Half-size cells, 125 instead of 27 per neighbourhood, were
+    // measured 3x slower -- 408 vs 137 us per pair launch, profiles/r2_notes.md -- and the knob is gone.)
     P.cells_per_cut = 1;
-    if (const char *env = getenv("GC_CELLS_PER_CUT")) P.cells_per_cut = std::max(1, atoi(env));
     {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
@@ -314,6 +315,9 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     if (!rc) rc = dev_alloc(ctx, &P.sref, RN);
     if (!rc) rc = dev_alloc(ctx, &P.scell, RN);
     if (!rc) rc = dev_alloc(ctx, &P.sab, RN);
+    P.n_units = (n_beads + 1) / 2 + 1;
+    P.unit_plane = (size_t) n_replicas * (size_t) P.n_units;
+    if (!rc) rc = dev_alloc(ctx, &P.punit, 3 * P.unit_plane);
     if (!rc) rc = dev_alloc(ctx, &P.members, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_of, RN);
     if (!rc) rc = dev_alloc(ctx, &P.cell_list, RN);
@@ -684,6 +688,19 @@ int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out)
     return GC_OK;
 }
 
+int gc_set_step(gc_ctx *ctx, int32_t replica, int64_t step)
+{
+    GC_CHECK_CTX(ctx);
+    if (step < 0) return fail(ctx, GC_ERR_INVALID, "step must be >= 0");
+    int rc = modify_states(ctx, replica, [&](RepState &st, int) {
+        st.step = step;
+        st.time = (double) step * ctx->hp.dt_cfg;
+    });
+    if (rc) return rc;
+    ctx->run_step = step;      // host mirror (contact cadence, graph alignment): replicas move in lockstep
+    return GC_OK;
+}
+
 int gc_get_contexts(gc_ctx *ctx, gc_context *out)
 {
     GC_CHECK_CTX(ctx);
@@ -930,28 +947,27 @@ __global__ void k_restart(const __grid_constant__ Params P, double dt)
     st.epoch += 1;        // a new logical run draws a new noise stream
 }
 
+// the pair kernel in the shape this launch needs (names kept short: the LAUNCH macro
+// stringifies them for the profiler)
+void launch_pair(gc_ctx *ctx, unsigned mask, int use_enabled)
+{
+    constexpr auto k_pair_cells_plain = k_pair_cells<true, GC_CELL_MINBLOCKS>;
+    constexpr auto k_pair_cells_ab = k_pair_cells<false, GC_CELL_MINBLOCKS>;
+    constexpr auto k_pair_cells_plain_dense = k_pair_cells<true, MINBLOCKS_DENSE>;
+    constexpr auto k_pair_cells_ab_dense = k_pair_cells<false, MINBLOCKS_DENSE>;
+    const bool plain = ctx->hp.pair.mode == PAIR_PLAIN;
+    if (plain && ctx->dense_pair) LAUNCH(ctx, k_pair_cells_plain_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    else if (plain) LAUNCH(ctx, k_pair_cells_plain, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    else if (ctx->dense_pair) LAUNCH(ctx, k_pair_cells_ab_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+    else LAUNCH(ctx, k_pair_cells_ab, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
+}
+
 // one force evaluation (+ update when fused) for every replica
 // fuse_rebuild (fixed dt, small path): the epilogue also builds the NEXT step's cell list
 void launch_step(gc_ctx *ctx, int mode, unsigned mask, int use_enabled, bool fuse_rebuild = false)
 {
     // (the macro stringifies its kernel argument for the profiler: keep the names short)
-    constexpr auto k_pair_cells_plain = k_pair_cells<true, GC_CELL_MINBLOCKS>;
-    constexpr auto k_pair_cells_ab = k_pair_cells<false, GC_CELL_MINBLOCKS>;
-    constexpr auto k_pair_cells_plain_dense = k_pair_cells<true, MINBLOCKS_DENSE>;
-    constexpr auto k_pair_cells_ab_dense = k_pair_cells<false, MINBLOCKS_DENSE>;
-    if (ctx->hp.pair.mode == PAIR_PLAIN) {
-        if (ctx->dense_pair) {
-            LAUNCH(ctx, k_pair_cells_plain_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
-        } else {
-            LAUNCH(ctx, k_pair_cells_plain, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
-        }
-    } else {
-        if (ctx->dense_pair) {
-            LAUNCH(ctx, k_pair_cells_ab_dense, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
-        } else {
-            LAUNCH(ctx, k_pair_cells_ab, ctx->tile_grid_x, CW * 32, ctx->hp, mask, use_enabled);
-        }
-    }
+    launch_pair(ctx, mask, use_enabled);
     dim3 gf = bead_grid(ctx, BS);
     const int gr = ctx->n_rep;
     if (mode == STEP_FUSED) {
@@ -983,6 +999,7 @@ Params params_window(const Params &P, int r0, int nr)
     W.sref += o;
     W.scell += o;
     W.sab += o;
+    W.punit += (size_t) r0 * (size_t) P.n_units;      // the plane stride stays
     W.members += o;
     W.cell_of += o;
     W.cell_list += o;
@@ -1920,11 +1937,7 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     }
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
-    if (ctx->hp.pair.mode == PAIR_PLAIN) {
-        LAUNCH(ctx, (k_pair_cells<true, GC_CELL_MINBLOCKS>), ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
-    } else {
-        LAUNCH(ctx, (k_pair_cells<false, GC_CELL_MINBLOCKS>), ctx->tile_grid_x, CW * 32, ctx->hp, 0u, 1);
-    }
+    launch_pair(ctx, 0u, 1);
     const int owned = P.own_hi - P.own_lo;
     LAUNCH(ctx, k_finish<STEP_FUSED>, dim3(std::max((owned + BS - 1) / BS, 1), 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);

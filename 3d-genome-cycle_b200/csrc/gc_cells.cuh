@@ -1,5 +1,4 @@
-// gc_cells.cuh -- nonbonded soft-core forces, warp-per-cell (the production
-// pair kernel).
+// gc_cells.cuh -- nonbonded soft-core forces, warp-per-cell (the production pair kernel).
 //
 // Replaces the pair loop of md::neighbor_pairwise_forcefield
 // (MD/forcefield/neighbor_pairwise_forcefield.hpp:68-84) together with the
@@ -7,18 +6,17 @@
 // list exists here.  Each WARP pops non-empty home cells from a per-replica work
 // queue (Params::cell_list, filled by k_gather) and, privately, with no block
 // barrier anywhere:
-//   1. lanes 0..(2M+1)^2-1 fetch the slot ranges of the contiguous x-rows of the
-//      neighbouring cells (9 rows of 3 cells for M = 1; the grid carries an M-cell
-//      halo, so there are no bounds checks); a warp scan flattens them into one
-//      candidate list;
-//   2. the warp stages that list into ITS OWN shared-memory tile, coalesced per
-//      row, as (x, y, z, A') + B' with the A/B mixing factors pre-scaled;
+//   1. lanes 0..8 fetch the slot ranges of the 9 contiguous x-rows of 3 neighbouring
+//      cells (the grid carries a one-cell halo, so there are no bounds checks) and turn
+//      them into disjoint ranges of 48-byte candidate UNITS (two sorted slots each);
+//   2. the warp stages the units into ITS OWN shared-memory tile, 32 units (64
+//      candidates) per iteration: 3 LDG.128, one packed bounding-box cull of both beads,
+//      ballot compaction, 3 STS.128;
 //   3. lanes split into H home beads x S candidate slices (H * S <= 32, chosen per
 //      cell; cells with more than 16 beads are served in groups of 16, each with its own
 //      culled tile) and evaluate EVERY staged candidate branch-free: the clamped soft
 //      cores vanish identically beyond their diameter, so there is no distance
-//      test, no ballot and no compaction (packed FP32x2 math, 16.5 issued
-//      instructions per pair);
+//      test, no ballot and no compaction in the loop (packed FP32x2 math);
 //   4. S - 1 shuffles per component fold the slices and lanes < H store the force
 //      of their home bead (sorted-slot order, consumed by k_finish).
 // Every bead gathers its own force (full neighbourhood, no atomics), so the
@@ -38,11 +36,7 @@ constexpr int CW = 4;                    // warps per block
 #ifndef GC_CELL_MINBLOCKS
 #define GC_CELL_MINBLOCKS 8
 #endif
-#ifndef GC_PACK_UNROLL
-#define GC_PACK_UNROLL 2
-#endif
-constexpr int kPackUnroll = GC_PACK_UNROLL;   // candidate pairs in flight per lane
-constexpr int CCAP = GC_CCAP;            // candidates per tile chunk
+constexpr int CCAP = GC_CCAP;            // candidates per tile chunk of the contact kernel
 // kRecip[d] = 65536 / d + 1: x / d == (x * kRecip[d]) >> 16 for x * d < 65536 (lane splits,
 // slice counts and tile lengths are all far below); index 0 is unused
 __constant__ unsigned int kRecip[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
@@ -51,37 +45,13 @@ __constant__ unsigned int kRecip[33] = {0, 65537, 32769, 21846, 16385, 13108, 10
 // few cells with more than 16 beads, and the per-group bounding box culls tighter.)
 constexpr int CHMAX = 16;
 
-// One soft-core pair, branchless (see header).  sA = 0.5 cA (a_i + a_j) and
-// sB = 0.5 cB (b_i + b_j) arrive pre-scaled:
-//   A: 6 eps_A kA2 (1 - u)^2,  B: 24 eps_B kB2 (1 - u^4)^2 u^3   (gc_math.cuh)
-__device__ __forceinline__ void pair_accumulate(float xi, float yi, float zi, float Ai, float Bi,
-                                                float4 q, float Bj, float kA2, float kB2,
-                                                float &fx, float &fy, float &fz)
-{
-    const float ex = xi - q.x, ey = yi - q.y, ez = zi - q.z;
-    const float r2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
-    const float gA = fmaxf(fmaf(-r2, kA2, 1.0f), 0.0f);
-    const float uB = r2 * kB2;
-    const float uB2 = uB * uB;
-    const float gB = fmaxf(fmaf(-uB2, uB2, 1.0f), 0.0f);
-    const float tA = gA * gA;
-    const float tB = (gB * gB) * (uB2 * uB);
-    const float fac = fmaf(Bi + Bj, tB, (Ai + q.w) * tA);
-    fx = fmaf(fac, ex, fx);
-    fy = fmaf(fac, ey, fy);
-    fz = fmaf(fac, ez, fz);
-}
-
-// The tile is stored as PAIRS of candidates per component so that the hot loop can
-// use Blackwell's packed FP32x2 instructions (fma.rn.f32x2 & co., SASS FFMA2 / FMUL2 /
-// FADD2): the FP32 pipe still retires 128 lanes per clock, but every issued
-// instruction now carries two pair evaluations, which takes the kernel off the
-// issue-slot limit (profiles/r1_notes.md).
+// Per-warp shared-memory tile of the contact kernel (gc_contact.cuh): candidates staged
+// component-wise, plus the row tables of its flattening walk.
 template<int CAP>
 struct CellWarpSmemT {
     static_assert(CAP % 2 == 0, "candidates are staged in pairs");
     float2 tx[CAP / 2], ty[CAP / 2], tz[CAP / 2];
-    float2 tA[CAP / 2], tB[CAP / 2];     // pre-scaled mixing factors A', B'
+    float2 tA[CAP / 2], tB[CAP / 2];     // bead index of the candidate / ring of queued hits
     int row_off[33];                     // first flattened index of each row (+ sentinel)
     int row_shift[32];                   // slot = flattened index + row_shift[row]
 };
@@ -89,66 +59,13 @@ using CellWarpSmem = CellWarpSmemT<CCAP>;
 // The pair kernel exists in two shapes: GC_CELL_MINBLOCKS = 8 resident blocks per SM (64
 // registers) for launches that own the GPU, and 10 (48 registers) for the replica-group
 // branches of the step graph, where several pair kernels share the SMs and the extra
-// resident warps pay (profiles/r1_notes.md).  Both use the same 256-candidate tile
-// (10 blocks x 21 KB fit an SM), hence the same chunking of long candidate lists and the same
-// summation order: a trajectory does not depend on which shape ran a step.
-#ifndef GC_PAIR_CAP
-#define GC_PAIR_CAP 256
-#endif
+// resident warps pay (profiles/r1_notes.md).  Both use the same tile size, hence the same
+// chunking of long candidate lists and the same summation order: a trajectory does not
+// depend on which shape ran a step.
 #ifndef GC_DENSE_MINBLOCKS
 #define GC_DENSE_MINBLOCKS 10
 #endif
-constexpr int PAIR_CAP = GC_PAIR_CAP, MINBLOCKS_DENSE = GC_DENSE_MINBLOCKS;
-
-__device__ __forceinline__ float2 neg2(float2 v) { return make_float2(-v.x, -v.y); }
-__device__ __forceinline__ float2 max0(float2 v) { return make_float2(fmaxf(v.x, 0.0f), fmaxf(v.y, 0.0f)); }
-
-// Home-bead pass over the staged tile [0, nt): lanes = H beads x S slices; slice s
-// takes candidate pairs s, s + S, s + 2 S, ... (packed math), then the ragged tail
-// one candidate at a time.
-template<class SM>
-__device__ __forceinline__ void cell_pass(const SM &sm, int nt, int S, int s,
-                                          float4 me, float Ai, float Bi, float kA2, float kB2,
-                                          float &fx, float &fy, float &fz)
-{
-    // iterations in which every slice has a whole pair: (nt / 2) / S by reciprocal
-    // multiplication (exact for nt / 2 <= 2047, S <= 32)
-    const int full = (int) (((unsigned) (nt >> 1) * kRecip[S]) >> 16);
-    const float2 xi = make_float2(me.x, me.x), yi = make_float2(me.y, me.y), zi = make_float2(me.z, me.z);
-    const float2 Ai2 = make_float2(Ai, Ai), Bi2 = make_float2(Bi, Bi);
-    const float2 nkA = make_float2(-kA2, -kA2), kB = make_float2(kB2, kB2), one = make_float2(1.0f, 1.0f);
-    float2 ax = make_float2(0.f, 0.f), ay = ax, az = ax;
-#pragma unroll kPackUnroll
-    for (int it = 0; it < full; it++) {
-        const int p = s + it * S;
-        const float2 ex = __fadd2_rn(xi, neg2(sm.tx[p]));
-        const float2 ey = __fadd2_rn(yi, neg2(sm.ty[p]));
-        const float2 ez = __fadd2_rn(zi, neg2(sm.tz[p]));
-        const float2 r2 = __ffma2_rn(ex, ex, __ffma2_rn(ey, ey, __fmul2_rn(ez, ez)));
-        const float2 gA = max0(__ffma2_rn(r2, nkA, one));
-        const float2 uB = __fmul2_rn(r2, kB);
-        const float2 uB2 = __fmul2_rn(uB, uB);
-        const float2 gB = max0(__ffma2_rn(neg2(uB2), uB2, one));
-        const float2 tA = __fmul2_rn(gA, gA);
-        const float2 tB = __fmul2_rn(__fmul2_rn(gB, gB), __fmul2_rn(uB2, uB));
-        const float2 fac = __ffma2_rn(__fadd2_rn(Bi2, sm.tB[p]), tB,
-                                      __fmul2_rn(__fadd2_rn(Ai2, sm.tA[p]), tA));
-        ax = __ffma2_rn(fac, ex, ax);
-        ay = __ffma2_rn(fac, ey, ay);
-        az = __ffma2_rn(fac, ez, az);
-    }
-    fx += ax.x + ax.y;
-    fy += ay.x + ay.y;
-    fz += az.x + az.y;
-    // ragged tail: candidates [2 full S, nt), fewer than 2 S + 1 of them
-    const float *sx = reinterpret_cast<const float *>(sm.tx), *sy = reinterpret_cast<const float *>(sm.ty);
-    const float *sz = reinterpret_cast<const float *>(sm.tz), *sA = reinterpret_cast<const float *>(sm.tA);
-    const float *sB = reinterpret_cast<const float *>(sm.tB);
-    for (int k = 2 * full * S + s; k < nt; k += S) {
-        pair_accumulate(me.x, me.y, me.z, Ai, Bi, make_float4(sx[k], sy[k], sz[k], sA[k]), sB[k], kA2,
-                        kB2, fx, fy, fz);
-    }
-}
+constexpr int MINBLOCKS_DENSE = GC_DENSE_MINBLOCKS;
 
 // Sum over the S slices of each home bead, in fixed order; valid in lanes < H.
 __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, float &fy, float &fz)
@@ -162,14 +79,119 @@ __device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, flo
     }
 }
 
+// ---------------------------------------------------------------------------
+// The production pair kernel (round 2).  Same algorithm as round 1's kernel; what changed
+// is the data movement.  ncu on that kernel (profiles/r1_pair_cells_v8_sparse_ncu_summary.txt) and on
+// two intermediate kernels (profiles/r2_pair_cells_v9_*, r2_pair_bulk_rejected_*): 43 % of the
+// instructions were per-cell set-up, 34-45 % moved candidates one at a time through registers
+// (flatten -> LDG -> cull -> ballot -> 5 st.shared each), 24 % were the pair loop.
+//   * k_gather leaves, beside the sorted float4 positions, a PAIR-INTERLEAVED copy of the
+//     sorted beads, one 48-byte unit per two slots (2u, 2u + 1):
+//         (x0 x1 y0 y1) (z0 z1 a0 a1) (b0 b1 - -)
+//     -- exactly the operand layout of the packed FP32x2 pair loop.  Staging moves UNITS:
+//     3 LDG.128 in, one packed bounding-box test for both beads, 3 STS.128 out, for 64
+//     candidates per warp iteration (was 32, at 2.5 x the instructions).
+//   * the 9 candidate rows become disjoint unit ranges (rows may touch in slot space); the
+//     flattened unit index is mapped to its row by a 4-step binary search over the row ends,
+//     which stay in lanes 0..15 (shuffles, no shared-memory tables, no per-lane walk).
+//     A unit may carry one bead of a cell OUTSIDE the 27 at the outer end of a run of rows;
+//     it lies more than a cell edge >= cutoff from the home cell, where both clamped soft
+//     cores are exactly zero (and it usually fails the cull anyway).
+//   * the loop evaluates e' = x_j - x_i against the negated home position, the clamps are
+//     min(g', 0) with g' = -g: no operand negation per pair; the sum is negated once.
+//   * every slice runs `for (m = s; m < units; m += S)`: no reciprocal trip count, no scalar
+//     tail loop (the unused half of an odd last unit is a far dummy written by k_gather).
+//   * the home bounding box is reduced on the raw bits of (x - origin) >= 0: one REDUX per
+//     bound.
+// A bulk-async-copy variant (cp.async.bulk of whole rows onto an mbarrier, no culling) was
+// built and measured slower: see profiles/r2_notes.md.
+// ---------------------------------------------------------------------------
+#ifndef GC_TILE_UNITS
+#define GC_TILE_UNITS 112
+#endif
+constexpr int TILE_UNITS = GC_TILE_UNITS;        // candidate pairs per tile chunk (48 bytes each)
+
+struct PairUnit {
+    float4 xy, zA, B;
+};
+static_assert(sizeof(PairUnit) == 48, "unit layout");
+
+// One home bead against one candidate unit (two candidates, packed).
+template<bool PLAIN>
+__device__ __forceinline__ void unit_eval(float4 a, float4 b, float2 bj, float nx, float ny, float nz,
+                                          float Ai, float Bi, float2 kA, float2 kB, float2 &ax,
+                                          float2 &ay, float2 &az)
+{
+    const float2 mone = make_float2(-1.0f, -1.0f);
+    const float2 ex = __fadd2_rn(make_float2(a.x, a.y), make_float2(nx, nx));       // e' = x_j - x_i
+    const float2 ey = __fadd2_rn(make_float2(a.z, a.w), make_float2(ny, ny));
+    const float2 ez = __fadd2_rn(make_float2(b.x, b.y), make_float2(nz, nz));
+    const float2 r2 = __ffma2_rn(ex, ex, __ffma2_rn(ey, ey, __fmul2_rn(ez, ez)));
+    float2 gA = __ffma2_rn(r2, kA, mone);                           // -(1 - r2 kA2)
+    gA = make_float2(fminf(gA.x, 0.0f), fminf(gA.y, 0.0f));
+    float2 fac = __fmul2_rn(__fadd2_rn(make_float2(Ai, Ai), make_float2(b.z, b.w)), __fmul2_rn(gA, gA));
+    if (!PLAIN) {
+        const float2 uB = __fmul2_rn(r2, kB);
+        const float2 uB2 = __fmul2_rn(uB, uB);
+        float2 gB = __ffma2_rn(uB2, uB2, mone);                     // -(1 - uB^4)
+        gB = make_float2(fminf(gB.x, 0.0f), fminf(gB.y, 0.0f));
+        const float2 tB = __fmul2_rn(__fmul2_rn(gB, gB), __fmul2_rn(uB2, uB));
+        fac = __ffma2_rn(__fadd2_rn(make_float2(Bi, Bi), bj), tB, fac);
+    }
+    ax = __ffma2_rn(fac, ex, ax);
+    ay = __ffma2_rn(fac, ey, ay);
+    az = __ffma2_rn(fac, ez, az);
+}
+
+// Home beads of one lane: TWO, so that every unit fetched from shared memory serves four pair
+// evaluations.  (With one bead per lane the loop was bound by the shared-memory data pipe,
+// not by issue: ncu l1tex__data_pipe_lsu_wavefronts 69 % of peak, issue 61 %; an LDS.128
+// costs four wavefronts however many lanes share an address.)
+#ifndef GC_HOME_PER_LANE
+#define GC_HOME_PER_LANE 1
+#endif
+constexpr int HB = GC_HOME_PER_LANE;     // home beads per lane (1 or 2)
+#ifndef GC_PASS_UNROLL
+#define GC_PASS_UNROLL (HB == 1 ? 2 : 1)
+#endif
+constexpr int kPassUnroll = GC_PASS_UNROLL;
+struct HomePair {
+    float nx[HB], ny[HB], nz[HB], A[HB], B[HB];
+    float2 ax[HB], ay[HB], az[HB];
+};
+
+// lanes = H2 home-bead groups (HB beads each) x S slices; slice s takes units s, s + S, ...
+template<bool PLAIN>
+__device__ __forceinline__ void unit_pass(const PairUnit *tile, int nu, int S, int s, float kA2, float kB2,
+                                          HomePair &h)
+{
+    const float2 kA = make_float2(kA2, kA2), kB = make_float2(kB2, kB2);
+#pragma unroll kPassUnroll
+    for (int m = s; m < nu; m += S) {
+        const float4 a = tile[m].xy;
+        const float4 b = tile[m].zA;
+        float2 bj = make_float2(0.f, 0.f);
+        if (!PLAIN) bj = *reinterpret_cast<const float2 *>(&tile[m].B);
+#pragma unroll
+        for (int j = 0; j < HB; j++) {
+            unit_eval<PLAIN>(a, b, bj, h.nx[j], h.ny[j], h.nz[j], h.A[j], h.B[j], kA, kB, h.ax[j], h.ay[j], h.az[j]);
+        }
+    }
+}
+
+#ifndef GC_TICKET
+#define GC_TICKET 1
+#endif
+constexpr int TICKET = GC_TICKET;       // cells per work-queue claim (1 or 2)
+static_assert(TICKET == 1 || TICKET == 2, "cells per claim");
+constexpr int CH2MAX = 16 * HB;          // home beads per staged tile (16 lanes x HB)
+
 template<bool PLAIN, int MINB>
 __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
                                                         int use_enabled)
 {
     GC_PDL_ENTRY();
-    constexpr int CAP = PAIR_CAP;
-    using CellSmem = CellWarpSmemT<CAP>;
-    __shared__ CellSmem s_warp[CW];
+    __shared__ __align__(16) PairUnit s_tile[CW][TILE_UNITS];
 
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -184,20 +206,11 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
         return;
     }
 
-    const int M = P.cells_per_cut;
-    const int side = 2 * M + 1, nrows = side * side;
-    constexpr bool plain = PLAIN;          // one soft core, no A/B mixing (mitotic stages)
-    CellSmem &sm = s_warp[warp];
-    // tx, ty, tz, tA, tB are consecutive arrays of CAP floats (static_assert below)
-    const unsigned tile_addr = (unsigned) __cvta_generic_to_shared(sm.tx);
-    static_assert(offsetof(CellSmem, ty) == sizeof(float2) * (CAP / 2) &&
-                  offsetof(CellSmem, tz) == 2 * sizeof(float2) * (CAP / 2) &&
-                  offsetof(CellSmem, tA) == 3 * sizeof(float2) * (CAP / 2) &&
-                  offsetof(CellSmem, tB) == 4 * sizeof(float2) * (CAP / 2), "tile layout");
+    PairUnit *tile = s_tile[warp];
+    const unsigned lt_mask = (1u << lane) - 1u;
 
     // Blocks are not tied to a replica: every warp works through the queues of all
-    // replicas round-robin, starting at a different one, so an ensemble is balanced
-    // across the whole GPU whatever part of the grid is resident.
+    // replicas round-robin, starting at a different one.
     for (int rr = 0; rr < P.n_rep; rr++) {
     const int r = (blockIdx.x + rr) % P.n_rep;
     RepState &st = P.st[r];
@@ -205,136 +218,175 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
     const size_t ro = (size_t) r * P.n;
     const float4 *__restrict__ sp = P.spos[st.parity] + ro;
     const float2 *__restrict__ sab = P.sab + ro;
+    const float4 *__restrict__ uxy = P.punit + (size_t) r * P.n_units;
+    const float4 *__restrict__ uzA = uxy + P.unit_plane;
+    const float4 *__restrict__ uB = uzA + P.unit_plane;
     float4 *__restrict__ pforce = P.pforce + ro;
     const int *__restrict__ start = P.cell_start + (size_t) r * (P.ncell_max + 1);
     const int4 *__restrict__ cells = P.cell_list + ro;
     const int nheavy = st.n_used_cells, nused = nheavy + st.n_light_cells;
     const int dx = st.dims[0], dxy = st.dims[0] * st.dims[1];
-    const float kA2 = sc.kA2, kB2 = sc.kB2;
-    const float hA = 0.5f * sc.cA, hB = plain ? 0.0f : 0.5f * sc.cB;
+    const float kA2 = sc.kA2, kB2 = PLAIN ? 0.0f : sc.kB2;
+    const float hA = 0.5f * sc.cA, hB = PLAIN ? 0.0f : 0.5f * sc.cB;
     // squared cutoff of the pair term (the larger soft core), with a hair of margin
-    const float cull2 = 1.0002f / (plain ? kA2 : fminf(kA2, kB2));
-    const unsigned lt_mask = (1u << lane) - 1u;
-    // row `lane` of the (2M+1)^2 neighbour rows, relative to the home cell: the
-    // grid has an M-cell halo (plan_grid), so every row exists
-    const int row_rel = lane < nrows ? (lane % side - M) * dx + (lane / side - M) * dxy - M : 0;
+    const float cull2 = 1.0002f / (PLAIN ? kA2 : fminf(kA2, kB2));
+    const float ox = st.origin[0], oy = st.origin[1], oz = st.origin[2];
+    // row `lane` of the 9 neighbour rows (dy, dz in -1..1), relative to the home cell; the
+    // grid has a one-cell halo (plan_grid), so every row exists
+    const int row_rel = lane < 9 ? (lane % 3 - 1) * dx + (lane / 3 - 1) * dxy - 1 : 0;
 
     for (;;) {
-        int kk = 0;
-        if (lane == 0) kk = atomicAdd(&st.cell_cursor, 1);
-        kk = __shfl_sync(0xffffffffu, kk, 0);
-        if (kk >= nused) break;
-        const int4 cell = __ldg(&cells[kk < nheavy ? kk : P.n - 1 - (kk - nheavy)]);
-        const int c = cell.x, h0 = cell.y, nhome = cell.z;
-
-        // ---- 1. candidate rows -> flattened list -------------------------------
-        int lo = 0, len = 0;
-        if (lane < nrows) {
-            lo = __ldg(&start[c + row_rel]);
-            len = __ldg(&start[c + row_rel + side]) - lo;
+        // Work queue: GC_TICKET cells per claim.  The dependent chain ticket -> cell
+        // descriptor -> row starts (three L2 round trips) is paid once per claim, and the
+        // loads of the second cell are in flight while the first is evaluated.
+        int kk0 = 0;
+        if (lane == 0) kk0 = atomicAdd(&st.cell_cursor, TICKET);
+        kk0 = __shfl_sync(0xffffffffu, kk0, 0);
+        if (kk0 >= nused) break;
+        // (scalars, not arrays: the second cell's five values stay in registers)
+        const int kA_ = kk0, kB_ = min(kk0 + 1, nused - 1);
+        const int4 cellA = __ldg(&cells[kA_ < nheavy ? kA_ : P.n - 1 - (kA_ - nheavy)]);
+        int4 cellB = cellA;
+        if (TICKET == 2) cellB = __ldg(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
+        int loA = 0, u1A = 0, loB = 0, u1B = 0;
+        if (lane < 9) {
+            loA = __ldg(&start[cellA.x + row_rel]);
+            u1A = (__ldg(&start[cellA.x + row_rel + 3]) + 1) >> 1;
+            if (TICKET == 2) {
+                loB = __ldg(&start[cellB.x + row_rel]);
+                u1B = (__ldg(&start[cellB.x + row_rel + 3]) + 1) >> 1;
+            }
         }
-        int incl = len;
+        int h0 = cellA.y, nhome = cellA.z, lo = loA, u1 = u1A;
+#pragma unroll 1
+        for (int t = 0; t < TICKET && kk0 + t < nused; t++) {
+        if (t == 1) { h0 = cellB.y; nhome = cellB.z; lo = loB; u1 = u1B; }
+
+        // ---- 1. candidate rows as DISJOINT unit ranges ------------------------------
+        // Rows ascend in slot space and may touch (everything between two rows empty): a
+        // row starts no earlier than its predecessor ended, so the union covers every unit
+        // that holds a bead of the 27 cells exactly once.
+        const int prev = __shfl_up_sync(0xffffffffu, u1, 1);
+        const int u0 = max(lo >> 1, lane > 0 ? prev : 0);
+        const int nu = lane < 9 ? max(u1 - u0, 0) : 0;
+        int incl = nu;                                         // lanes 9..15 end up holding U
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
+        for (int o = 1; o < 16; o <<= 1) {
             const int v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += v;
         }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        __syncwarp();                                          // previous cell fully consumed
-        sm.row_off[lane] = incl - len;                         // lanes >= nrows hold `total`
-        sm.row_shift[lane] = lo - (incl - len);
-        if (lane == 0) sm.row_off[32] = total;
-        __syncwarp();
+        const int U = __shfl_sync(0xffffffffu, incl, 8);
+        const int shift = u0 - (incl - nu);                    // unit = flattened index + shift(row)
+        const int last = U - 1;
 
-        for (int g0 = 0; g0 < nhome; g0 += CHMAX) {            // home beads, <= 16 per tile
-            const int ng = min(CHMAX, nhome - g0);
-            // lanes = ng home beads x S candidate slices
-            const unsigned rh = kRecip[ng];
+        for (int g0 = 0; g0 < nhome; g0 += CH2MAX) {           // home beads, <= 32 per pass
+            const int ng = min(CH2MAX, nhome - g0);
+            // lanes = H2 home-bead pairs x S candidate slices
+            const int H2 = (ng + HB - 1) / HB;
+            const unsigned rh = kRecip[H2];
             const int S = (int) ((32u * rh) >> 16);
-            const int sl = (int) (((unsigned) lane * rh) >> 16), hl = lane - sl * ng;
-            const float4 me = __ldg(&sp[h0 + g0 + hl]);
-            float Ai = hA, Bi = 0.0f;
-            if (!plain) {
-                const float2 abi = __ldg(&sab[h0 + g0 + hl]);
-                Ai = hA * abi.x; Bi = hB * abi.y;
-            }
-            float fx = 0.f, fy = 0.f, fz = 0.f;
+            const int sl = (int) (((unsigned) lane * rh) >> 16), hl = lane - sl * H2;
 
-            // ---- 2. stage: flattened, coalesced within each row, culled, compacted --------
-            // The loads of the next 32 candidates are issued before the current 32 are
-            // tested and stored (and before the home beads' bounding box is reduced).
-            // (tail lanes re-read the last candidate and are masked out of the ballot, so the
-            // loop body has no predicated blocks)
-            int kin = 0, row = 0, end = sm.row_off[1], shift = sm.row_shift[0];
-            float4 qn;
-            float2 abn = make_float2(0.f, 0.f);
-            const int last = total - 1;
-            auto fetch = [&](int k0) {
-                const int k = min(k0 + lane, last);
-                if (k >= end) {
-                    do {
-                        row++;
-                        end = sm.row_off[row + 1];
-                    } while (k >= end);
-                    shift = sm.row_shift[row];
-                }
-                qn = __ldg(&sp[k + shift]);
-                if (!plain) abn = __ldg(&sab[k + shift]);
-            };
-            fetch(0);
             // Bounding box of this group's home beads: a candidate further than the cutoff
-            // from the box is further than the cutoff from every home bead, where both
-            // clamped soft cores are exactly zero -- it is dropped while staging, which
-            // removes 35-45 % of the branch-free pair evaluations.
-            float blo[3], bhi[3];
+            // from the box is further than the cutoff from every home bead, where the clamped
+            // soft cores are exactly zero.  x - origin >= one cell edge > 0 for every bead
+            // (plan_grid puts the origin a cell below the bounding box), so the raw bits of
+            // the shifted coordinates order like the floats: one REDUX per bound.
+            float2 blx, bly, blz, bhx, bhy, bhz;
             {
                 const float4 hp = __ldg(&sp[h0 + g0 + min(lane, ng - 1)]);
-                blo[0] = ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(hp.x)));
-                blo[1] = ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(hp.y)));
-                blo[2] = ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(hp.z)));
-                bhi[0] = ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(hp.x)));
-                bhi[1] = ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(hp.y)));
-                bhi[2] = ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(hp.z)));
+                const unsigned ux = __float_as_uint(hp.x - ox), uy = __float_as_uint(hp.y - oy);
+                const unsigned uz = __float_as_uint(hp.z - oz);
+                float v;
+                v = __uint_as_float(__reduce_min_sync(0xffffffffu, ux)) + ox; blx = make_float2(v, v);
+                v = __uint_as_float(__reduce_min_sync(0xffffffffu, uy)) + oy; bly = make_float2(v, v);
+                v = __uint_as_float(__reduce_min_sync(0xffffffffu, uz)) + oz; blz = make_float2(v, v);
+                v = -(__uint_as_float(__reduce_max_sync(0xffffffffu, ux)) + ox); bhx = make_float2(v, v);
+                v = -(__uint_as_float(__reduce_max_sync(0xffffffffu, uy)) + oy); bhy = make_float2(v, v);
+                v = -(__uint_as_float(__reduce_max_sync(0xffffffffu, uz)) + oz); bhz = make_float2(v, v);
             }
+            HomePair hm;
+#pragma unroll
+            for (int j = 0; j < HB; j++) hm.ax[j] = hm.ay[j] = hm.az[j] = make_float2(0.f, 0.f);
+
+            // ---- 2. stage: flattened units, culled by the box, compacted ------------------
             int nt = 0;
-            while (kin < total) {
-                const float4 q = qn;
-                const float2 ab = abn;
-                const bool v = kin + lane < total;
-                kin += 32;
-                if (kin < total) fetch(kin);
-                const float ex = fmaxf(fmaxf(blo[0] - q.x, q.x - bhi[0]), 0.0f);
-                const float ey = fmaxf(fmaxf(blo[1] - q.y, q.y - bhi[1]), 0.0f);
-                const float ez = fmaxf(fmaxf(blo[2] - q.z, q.z - bhi[2]), 0.0f);
+            for (int kin = 0; kin < U; kin += 32) {
+                const int k = min(kin + lane, last);
+                // row of k = number of row ends <= k: binary search over the ends held in
+                // lanes 0..15 (4 shuffles), then the row's shift (1 shuffle)
+                int row = 0;
+#pragma unroll
+                for (int step = 8; step > 0; step >>= 1) {
+                    const int t = __shfl_sync(0xffffffffu, incl, row + step - 1);
+                    row += k >= t ? step : 0;
+                }
+                const int u = k + __shfl_sync(0xffffffffu, shift, row);
+                const float4 a = __ldg(&uxy[u]);
+                float4 b = __ldg(&uzA[u]);
+                float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!PLAIN) bb = __ldg(&uB[u]);
+                // distance of both beads of the unit from the box (packed)
+                const float2 x2 = make_float2(a.x, a.y), y2 = make_float2(a.z, a.w), z2 = make_float2(b.x, b.y);
+                const float2 lx = __fadd2_rn(blx, make_float2(-x2.x, -x2.y)), hx = __fadd2_rn(x2, bhx);
+                const float2 ly = __fadd2_rn(bly, make_float2(-y2.x, -y2.y)), hy = __fadd2_rn(y2, bhy);
+                const float2 lz = __fadd2_rn(blz, make_float2(-z2.x, -z2.y)), hz = __fadd2_rn(z2, bhz);
+                const float2 ex = make_float2(fmaxf(fmaxf(lx.x, hx.x), 0.0f), fmaxf(fmaxf(lx.y, hx.y), 0.0f));
+                const float2 ey = make_float2(fmaxf(fmaxf(ly.x, hy.x), 0.0f), fmaxf(fmaxf(ly.y, hy.y), 0.0f));
+                const float2 ez = make_float2(fmaxf(fmaxf(lz.x, hz.x), 0.0f), fmaxf(fmaxf(lz.y, hz.y), 0.0f));
+                const float2 d2 = __ffma2_rn(ex, ex, __ffma2_rn(ey, ey, __fmul2_rn(ez, ez)));
 #ifdef GC_NO_CULL
-                const bool keep = v;
+                const bool keep = kin + lane < U;
 #else
-                const bool keep = v && fmaf(ex, ex, fmaf(ey, ey, ez * ez)) <= cull2;
+                const bool keep = (kin + lane < U) & (fminf(d2.x, d2.y) <= cull2);
 #endif
                 const unsigned m = __ballot_sync(0xffffffffu, keep);
                 if (keep) {
-                    // explicit shared-space stores: one address, five immediate offsets
-                    const unsigned a = tile_addr + 4u * (unsigned) (nt + __popc(m & lt_mask));
-                    constexpr unsigned kStride = (unsigned) (sizeof(float2) * (CAP / 2));
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(q.x) : "memory");
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + kStride), "f"(q.y) : "memory");
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 2 * kStride), "f"(q.z) : "memory");
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 3 * kStride), "f"(plain ? hA : hA * ab.x) : "memory");
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + 4 * kStride), "f"(plain ? 0.0f : hB * ab.y) : "memory");
+                    PairUnit *dst = tile + (nt + __popc(m & lt_mask));
+                    dst->xy = a;
+                    b.z = PLAIN ? hA : hA * b.z;               // A' = 1/2 cA a_j
+                    b.w = PLAIN ? hA : hA * b.w;
+                    dst->zA = b;
+                    if (!PLAIN) {
+                        bb.x *= hB;                            // B' = 1/2 cB b_j
+                        bb.y *= hB;
+                        dst->B = bb;
+                    }
                 }
                 nt += __popc(m);
-                if (nt > CAP - 32 || kin >= total) {          // tile full or input exhausted
+                if (nt > TILE_UNITS - 32 || kin + 32 >= U) {   // tile full or input exhausted
                     __syncwarp();
-                    // ---- 3. H home beads x S slices, branch-free -------------------
-                    cell_pass(sm, nt, S, sl, me, Ai, Bi, kA2, kB2, fx, fy, fz);
+                    // ---- 3. H2 home pairs x S slices, branch-free ---------------------
+                    // (the home beads' constants are loaded here, not before staging: their
+                    //  registers would otherwise be live across the staging loop)
+                    if (sl < S) {
+#pragma unroll
+                        for (int j = 0; j < HB; j++) {
+                            const int t = h0 + g0 + min(HB * hl + j, ng - 1);
+                            const float4 me = __ldg(&sp[t]);
+                            hm.nx[j] = -me.x; hm.ny[j] = -me.y; hm.nz[j] = -me.z;
+                            hm.A[j] = hA; hm.B[j] = 0.0f;
+                            if (!PLAIN) {
+                                const float2 abi = __ldg(&sab[t]);
+                                hm.A[j] = hA * abi.x; hm.B[j] = hB * abi.y;
+                            }
+                        }
+                        unit_pass<PLAIN>(tile, nt, S, sl, kA2, kB2, hm);
+                    }
                     __syncwarp();                              // tile fully consumed
                     nt = 0;
                 }
             }
-            // ---- 4. fold the slices, store -----------------------------------------
-            cell_fold(ng, S, lane, fx, fy, fz);
-            if (lane < ng) pforce[h0 + g0 + lane] = make_float4(fx, fy, fz, 0.0f);
+            // ---- 4. fold the slices, store (F_i = -sum fac e') ----------------------------
+#pragma unroll
+            for (int j = 0; j < HB; j++) {
+                float fx = -(hm.ax[j].x + hm.ax[j].y), fy = -(hm.ay[j].x + hm.ay[j].y);
+                float fz = -(hm.az[j].x + hm.az[j].y);
+                cell_fold(H2, S, lane, fx, fy, fz);
+                if (lane < H2 && HB * lane + j < ng) pforce[h0 + g0 + HB * lane + j] = make_float4(fx, fy, fz, 0.0f);
+            }
         }
+        }   // cells of this claim
     }
     }   // replicas
 }

@@ -353,7 +353,30 @@ __device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r
     P.spos[st.parity][ro + dst] = p;
     if (P.skin > 0.0f) P.sref[ro + dst] = p;
     P.scell[ro + dst] = c;
-    P.sab[ro + dst] = P.ab[idx];
+    const float2 ab = P.ab[idx];
+    P.sab[ro + dst] = ab;
+    {
+        // pair-interleaved copy (k_pair_cells stages whole units)
+        float *u0 = unit_half(P, r, dst, 0), *u1 = unit_half(P, r, dst, 1);
+        u0[0] = p.x;
+        u0[2] = p.y;
+        u1[0] = p.z;
+        u1[2] = ab.x;
+        unit_half(P, r, dst, 2)[0] = ab.y;
+        if (dst == P.n - 1) {
+            // the unused half of the last unit and the pad unit: a dummy bead 64 cells off
+            // the grid with zero mixing factors (finite r^2, force exactly 0)
+            const float fx = st.origin[0] - 64.0f * st.cell_size;
+            for (int t = P.n; t < 2 * P.n_units; t++) {
+                float *d0 = unit_half(P, r, t, 0), *d1 = unit_half(P, r, t, 1);
+                d0[0] = fx;
+                d0[2] = st.origin[1];
+                d1[0] = st.origin[2];
+                d1[2] = 0.0f;
+                unit_half(P, r, t, 2)[0] = 0.0f;
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P)

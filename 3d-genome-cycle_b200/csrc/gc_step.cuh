@@ -457,6 +457,12 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
         // displacement since the rebuild (neighbor_list.hpp:129-158)
         x.w = self4.w;
         P.spos[par ^ 1][ro + t] = x;
+        {   // ... and the pair-interleaved copy the pair kernel stages from
+            float *u0 = unit_half(P, r, t, 0);
+            u0[0] = x.x;
+            u0[2] = x.y;
+            unit_half(P, r, t, 1)[0] = x.z;
+        }
         float4 ref = P.sref[ro + t];
         float ex = x.x - ref.x, ey = x.y - ref.y, ez = x.z - ref.z;
         red.disp2 = fmaf(ex, ex, fmaf(ey, ey, ez * ez));

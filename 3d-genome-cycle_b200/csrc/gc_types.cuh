@@ -6,6 +6,8 @@
 //   sref   [R][N] float4   sorted positions at the last rebuild (skin > 0 only)
 //   scell  [R][N] int32    cell of each sorted slot (query kernels)
 //   sab    [R][N] float2   (a, b) factors gathered into sorted order
+//   punit  [3][R][N/2+1] float4  the same beads pair-interleaved: planes (x0 x1 y0 y1),
+//                           (z0 z1 a0 a1), (b0 b1 - -): what k_pair_cells stages, two beads at a time
 //   cell_count / cell_start [R][ncell_max(+1)] int32
 //   cell_list [R][N] int4   non-empty cells (the pair kernel's work queue)
 //   force  [R][N] float4   only for the adaptive stepper / gc_compute_force
@@ -198,6 +200,12 @@ struct Params {
     float4 *sref;
     int *scell;
     float2 *sab;
+    // pair-interleaved copy of the sorted beads for k_pair_cells (gc_cells.cuh): unit u =
+    // sorted slots 2u, 2u + 1 in three planes of [R][n_units] float4,
+    // (x0 x1 y0 y1), (z0 z1 a0 a1), (b0 b1 - -); plane k starts at punit + k * unit_plane
+    float4 *punit;
+    size_t unit_plane;
+    int n_units;                   // (n + 1) / 2 + 1 (one trailing pad unit)
     int *cell_count, *cell_start, *members, *cell_of;
     unsigned long long *scan_status;   // [R][scan_blocks] look-back words of k_scan
     int scan_blocks;               // ceil(ncell_max / SCAN_TILE)
@@ -228,6 +236,14 @@ struct Params {
     SourceTerm sources[GC_MAX_SOURCES];
     double poles[GC_MAX_POLES][3];
 };
+
+// first float of sorted slot `slot` of replica r in plane `plane` of Params::punit (the
+// second value of the same bead sits two floats further)
+__device__ __forceinline__ float *unit_half(const Params &P, int r, int slot, int plane)
+{
+    return reinterpret_cast<float *>(P.punit + (size_t) plane * P.unit_plane + (size_t) r * P.n_units +
+                                     (size_t) (slot >> 1)) + (slot & 1);
+}
 
 static_assert(sizeof(Params) <= 4000, "Params is passed by value as a kernel argument");
 

@@ -601,14 +601,16 @@ def run_b200_arm(args):
         if window is not None:
             km = window.nearest(WINDOW_STEPS / 2)
             g.set_positions(window.positions[km].astype(np.float64))
+            g.run(0, cfg.timestep, restart=True)                 # new noise stream, Wiener history reset
             g.set_context(**window.contexts[km])
-            prof_state = f"committed window state at step {window.steps[km]}"
+            g.set_step(window.steps[km])                         # resume the schedule at that step
+            prof_state = f"committed window state at step {window.steps[km]} + 64 steps"
         else:
             reset_to_t0()
             g.run(S, cfg.timestep, restart=True)
-            prof_state = f"t = 0 + {S} steps"
+            prof_state = f"t = 0 + {S + 64} steps"
         g.contacts_clear()
-        g.run(64, cfg.timestep, restart=True)                    # decorrelate the identical cells a little
+        g.run(64, cfg.timestep, restart=False)                   # decorrelate the identical cells a little
         g.profile_enable(True)
         g.run(args.profile_steps, cfg.timestep, restart=False)
         prof = g.profile_read()

@@ -225,6 +225,11 @@ int gc_set_schedule(gc_ctx *ctx, const gc_schedule *schedule);
 int gc_set_context(gc_ctx *ctx, int32_t replica, const gc_context *in);
 int gc_get_context(gc_ctx *ctx, int32_t replica, gc_context *out);
 
+/* Resume a logical run at `step` (replica = -1: all): the next gc_run with restart = 0
+   continues with step + 1, i.e. schedule time (step + 1) dt and Philox counter step + 1.
+   The reference cannot resume inside a stage (its checkpoint is the stage's last frame,
+   SURVEY section 5); here a saved frame + context + step is a mid-stage checkpoint. */
+int gc_set_step(gc_ctx *ctx, int32_t replica, int64_t step);
 /* Contexts of all replicas in one copy: out = [R]. */
 int gc_get_contexts(gc_ctx *ctx, gc_context *out);
 
