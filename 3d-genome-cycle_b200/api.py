@@ -116,6 +116,9 @@ SYMBOLS = [
                                     C.POINTER(C.c_size_t)]),
     ("gc_decomp_step_compute", C.c_int, [_P]),
     ("gc_decomp_step_commit", C.c_int, [_P]),
+    ("gc_transition_interphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, C.c_int32, _ip, C.c_int32]),
+    ("gc_transition_prometaphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, _ip, C.c_int32, _dp, C.c_int32]),
+    ("gc_transition_cycle", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, _dp, C.c_int32]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
@@ -482,6 +485,35 @@ class System:
 
     def decomp_step_commit(self):
         self._ck(self.lib.gc_decomp_step_commit(self._h))
+
+    # ---- inter-stage transitions on the device (self = destination context) -------
+    def transition_interphase_from(self, src, src_ranges, dst_ranges, copy_pairs=(), bits=16,
+                                   src_replica=0, dst_replica=0):
+        """telophase -> relaxation: spline resampling of every chain of `src` into self."""
+        a, b = _i(src_ranges).reshape(-1, 2), _i(dst_ranges).reshape(-1, 2)
+        cp = _i(copy_pairs).reshape(-1, 2)
+        self._ck(self.lib.gc_transition_interphase(src._h, src_replica, self._h, dst_replica, a.shape[0],
+                                                   _ptr(a, C.c_int32), _ptr(b, C.c_int32), cp.shape[0],
+                                                   _ptr(cp, C.c_int32) if cp.size else None, int(bits)))
+
+    def transition_prometaphase_from(self, src, src_ranges, target_ranges, sister_ranges, coarse_graining,
+                                     displacement, bits=16, src_replica=0, dst_replica=0):
+        """interphase -> prometaphase: centroid coarse-graining + displaced sister copy."""
+        a, t = _i(src_ranges).reshape(-1, 2), _i(target_ranges).reshape(-1, 2)
+        s = _i(sister_ranges).reshape(-1, 2) if sister_ranges is not None else None
+        d = _d(displacement)
+        self._ck(self.lib.gc_transition_prometaphase(src._h, src_replica, self._h, dst_replica, a.shape[0],
+                                                     _ptr(a, C.c_int32), _ptr(t, C.c_int32),
+                                                     _ptr(s, C.c_int32) if s is not None else None,
+                                                     int(coarse_graining), _ptr(d, C.c_double), int(bits)))
+
+    def transition_cycle_from(self, src, src_ranges, dst_ranges, displacement, bits=16, src_replica=0,
+                              dst_replica=0):
+        """prometaphase -> next anaphase: target chromatids displaced by -spindle_axis."""
+        a, b, d = _i(src_ranges).reshape(-1, 2), _i(dst_ranges).reshape(-1, 2), _d(displacement)
+        self._ck(self.lib.gc_transition_cycle(src._h, src_replica, self._h, dst_replica, a.shape[0],
+                                              _ptr(a, C.c_int32), _ptr(b, C.c_int32), _ptr(d, C.c_double),
+                                              int(bits)))
 
     # ---- observables / misc -----------------------------------------------
     def radius_of_gyration2(self, ranges, replica=0):

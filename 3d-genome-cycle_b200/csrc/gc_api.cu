@@ -24,6 +24,7 @@
 #include "gc_cells.cuh"
 #include "gc_contact.cuh"
 #include "gc_decomp.cuh"
+#include "gc_transition.cuh"
 #include "gc_peak.cuh"
 
 using namespace gc;
@@ -1952,6 +1953,165 @@ int gc_decomp_step_commit(gc_ctx *ctx)
     LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
     ctx->run_step++;
     ctx->parity ^= 1;
+    return GC_OK;
+}
+
+// ---------------------------------------------------------------------------
+// inter-stage transitions between two contexts of one device (gc_transition.cuh)
+// ---------------------------------------------------------------------------
+} // extern "C"
+
+namespace {
+
+// common checks + ordering: everything queued on src is done before dst's stream reads it
+int transition_begin(gc_ctx *src, int src_replica, gc_ctx *dst, int dst_replica, int n_chains,
+                     const float4 **sp, float4 **dp)
+{
+    if (!src || !dst) return GC_ERR_INVALID;
+    if (src->device != dst->device) return fail(dst, GC_ERR_INVALID, "contexts live on different devices");
+    if (src_replica < 0 || src_replica >= src->n_rep || dst_replica < 0 || dst_replica >= dst->n_rep ||
+        n_chains < 0) {
+        return fail(dst, GC_ERR_INVALID, "bad args");
+    }
+    GC_CUDA(dst, cudaSetDevice(dst->device));
+    GC_CUDA(dst, cudaStreamSynchronize(src->stream));
+    *sp = src->hp.pos[src->parity] + (size_t) src_replica * src->n;
+    *dp = dst->hp.pos[dst->parity] + (size_t) dst_replica * dst->n;
+    return GC_OK;
+}
+
+int check_ranges(gc_ctx *ctx, const int32_t *ranges, int n_chains, int n_beads, const char *what)
+{
+    for (int c = 0; c < n_chains; c++) {
+        if (ranges[2 * c] < 0 || ranges[2 * c + 1] < ranges[2 * c] || ranges[2 * c + 1] > n_beads) {
+            return fail(ctx, GC_ERR_INVALID, "%s range %d = [%d, %d) outside [0, %d)", what, c,
+                        ranges[2 * c], ranges[2 * c + 1], n_beads);
+        }
+    }
+    return GC_OK;
+}
+
+int upload_ints(gc_ctx *ctx, const int32_t *host, size_t count, int **dev)
+{
+    *dev = nullptr;
+    int rc = dev_alloc(ctx, dev, std::max<size_t>(count, 1));
+    if (rc) return rc;
+    if (count) {
+        GC_CUDA(ctx, cudaMemcpyAsync(*dev, host, count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return GC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int gc_transition_interphase(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                             int32_t n_chains, const int32_t *src_ranges, const int32_t *dst_ranges,
+                             int32_t n_copies, const int32_t *copy_pairs, int32_t fraction_bits)
+{
+    const float4 *sp;
+    float4 *dp;
+    int rc = transition_begin(src, src_replica, dst, dst_replica, n_chains, &sp, &dp);
+    if (rc) return rc;
+    if (!src_ranges || !dst_ranges || n_copies < 0 || (n_copies && !copy_pairs)) {
+        return fail(dst, GC_ERR_INVALID, "bad args");
+    }
+    if ((rc = check_ranges(dst, src_ranges, n_chains, src->n, "source")) != 0) return rc;
+    if ((rc = check_ranges(dst, dst_ranges, n_chains, dst->n, "destination")) != 0) return rc;
+    for (int k = 0; k < 2 * n_copies; k++) {
+        if (copy_pairs[k] < 0 || copy_pairs[k] >= dst->n) return fail(dst, GC_ERR_INVALID, "copy pair out of range");
+    }
+    int max_knots = 1;
+    for (int c = 0; c < n_chains; c++) max_knots = std::max(max_knots, src_ranges[2 * c + 1] - src_ranges[2 * c]);
+    const size_t smem = (size_t) 15 * max_knots * sizeof(double);
+    if (smem > 200u * 1024u) return fail(dst, GC_ERR_CAPACITY, "source chain of %d beads: spline does not fit shared memory", max_knots);
+    if (n_chains == 0) return GC_OK;
+    GC_CUDA(dst, cudaFuncSetAttribute(k_transition_spline, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    int *d_src = nullptr, *d_dst = nullptr, *d_cp = nullptr;
+    if ((rc = upload_ints(dst, src_ranges, 2 * (size_t) n_chains, &d_src)) != 0) return rc;
+    if ((rc = upload_ints(dst, dst_ranges, 2 * (size_t) n_chains, &d_dst)) != 0) return rc;
+    if ((rc = upload_ints(dst, copy_pairs, 2 * (size_t) n_copies, &d_cp)) != 0) return rc;
+    k_transition_spline<<<n_chains, 256, smem, dst->stream>>>(sp, dp, d_src, d_dst, max_knots, (int) fraction_bits);
+    dst->launches++;
+    if (n_copies) {
+        k_transition_copy<<<(n_copies + 127) / 128, 128, 0, dst->stream>>>(dp, d_cp, n_copies);
+        dst->launches++;
+    }
+    GC_CUDA(dst, cudaStreamSynchronize(dst->stream));
+    GC_CUDA(dst, cudaGetLastError());
+    dev_free(dst, d_src);
+    dev_free(dst, d_dst);
+    dev_free(dst, d_cp);
+    return GC_OK;
+}
+
+int gc_transition_prometaphase(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                               int32_t n_chains, const int32_t *src_ranges, const int32_t *target_ranges,
+                               const int32_t *sister_ranges, int32_t coarse_graining,
+                               const double displacement[3], int32_t fraction_bits)
+{
+    const float4 *sp;
+    float4 *dp;
+    int rc = transition_begin(src, src_replica, dst, dst_replica, n_chains, &sp, &dp);
+    if (rc) return rc;
+    if (!src_ranges || !target_ranges || coarse_graining < 1 || (sister_ranges && !displacement)) {
+        return fail(dst, GC_ERR_INVALID, "bad args");
+    }
+    if ((rc = check_ranges(dst, src_ranges, n_chains, src->n, "source")) != 0) return rc;
+    if ((rc = check_ranges(dst, target_ranges, n_chains, dst->n, "target")) != 0) return rc;
+    if (sister_ranges && (rc = check_ranges(dst, sister_ranges, n_chains, dst->n, "sister")) != 0) return rc;
+    int max_len = 0;
+    for (int c = 0; c < n_chains; c++) {
+        const int len = target_ranges[2 * c + 1] - target_ranges[2 * c];
+        if (sister_ranges && sister_ranges[2 * c + 1] - sister_ranges[2 * c] < len) {
+            return fail(dst, GC_ERR_INVALID, "sister chain %d shorter than its target", c);
+        }
+        max_len = std::max(max_len, len);
+    }
+    if (n_chains == 0 || max_len == 0) return GC_OK;
+    int *d_src = nullptr, *d_t = nullptr, *d_s = nullptr;
+    if ((rc = upload_ints(dst, src_ranges, 2 * (size_t) n_chains, &d_src)) != 0) return rc;
+    if ((rc = upload_ints(dst, target_ranges, 2 * (size_t) n_chains, &d_t)) != 0) return rc;
+    if (sister_ranges && (rc = upload_ints(dst, sister_ranges, 2 * (size_t) n_chains, &d_s)) != 0) return rc;
+    const double dx = displacement ? displacement[0] : 0.0, dy = displacement ? displacement[1] : 0.0;
+    const double dz = displacement ? displacement[2] : 0.0;
+    k_transition_coarse<<<dim3((max_len + 127) / 128, n_chains), 128, 0, dst->stream>>>(
+        sp, src->n, dp, n_chains, d_src, d_t, sister_ranges ? d_s : nullptr, (int) coarse_graining, dx, dy, dz,
+        (int) fraction_bits);
+    dst->launches++;
+    GC_CUDA(dst, cudaStreamSynchronize(dst->stream));
+    GC_CUDA(dst, cudaGetLastError());
+    dev_free(dst, d_src);
+    dev_free(dst, d_t);
+    if (d_s) dev_free(dst, d_s);
+    return GC_OK;
+}
+
+int gc_transition_cycle(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                        int32_t n_chains, const int32_t *src_ranges, const int32_t *dst_ranges,
+                        const double displacement[3], int32_t fraction_bits)
+{
+    const float4 *sp;
+    float4 *dp;
+    int rc = transition_begin(src, src_replica, dst, dst_replica, n_chains, &sp, &dp);
+    if (rc) return rc;
+    if (!src_ranges || !dst_ranges || !displacement) return fail(dst, GC_ERR_INVALID, "bad args");
+    if ((rc = check_ranges(dst, src_ranges, n_chains, src->n, "source")) != 0) return rc;
+    if ((rc = check_ranges(dst, dst_ranges, n_chains, dst->n, "destination")) != 0) return rc;
+    int max_len = 0;
+    for (int c = 0; c < n_chains; c++) max_len = std::max(max_len, dst_ranges[2 * c + 1] - dst_ranges[2 * c]);
+    if (n_chains == 0 || max_len == 0) return GC_OK;
+    int *d_src = nullptr, *d_dst = nullptr;
+    if ((rc = upload_ints(dst, src_ranges, 2 * (size_t) n_chains, &d_src)) != 0) return rc;
+    if ((rc = upload_ints(dst, dst_ranges, 2 * (size_t) n_chains, &d_dst)) != 0) return rc;
+    k_transition_shift<<<dim3((max_len + 127) / 128, n_chains), 128, 0, dst->stream>>>(
+        sp, dp, n_chains, d_src, d_dst, displacement[0], displacement[1], displacement[2], (int) fraction_bits);
+    dst->launches++;
+    GC_CUDA(dst, cudaStreamSynchronize(dst->stream));
+    GC_CUDA(dst, cudaGetLastError());
+    dev_free(dst, d_src);
+    dev_free(dst, d_dst);
     return GC_OK;
 }
 

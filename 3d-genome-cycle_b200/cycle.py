@@ -22,7 +22,10 @@ from .api import System
 
 
 def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_steps=1.0,
-                   log=None):
+                   log=None, frame_sink=None, host_transitions=False):
+    """frame_sink(system, frame): optional consumer of every sampled frame (e.g. a
+    store.TrajectoryWriter); host_transitions=True uses transitions.py (numpy / scipy on the
+    host) instead of the gc_transition_* kernels (A/B and tests)."""
     icfg = icfg or synth.InterphaseConfig()
     mcfg = mcfg or synth.MitoticConfig()
     design = design or synth.make_diploid_design(cfg=icfg)
@@ -37,20 +40,35 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
 
     def run_sampled(sys_, n, dt, interval, on_chunk=None):
         """n steps in chunks of the sampling interval; after each chunk the driver's
-        save_positions: one quantised f32 frame leaves the device (gc_get_frame)."""
+        save_positions: one quantised f32 frame leaves the device.  The frame is started
+        asynchronously (gc_frame_begin: quantise + copy on a second stream) and collected
+        after the NEXT chunk has been queued, so its transfer overlaps that chunk's steps."""
         done = 0
+        pending = False
+
+        def collect():
+            f = sys_.frame_end()
+            frames["count"] += 1
+            frames["bytes"] += f.nbytes
+            if frame_sink is not None:
+                frame_sink(sys_, f)
+
         if os.environ.get("GC_CYCLE_NO_FRAMES"):        # A/B: no frame output, window-sized chunks
             interval = max(interval, 10 * interval)
         while done < n:
             chunk = min(interval, n - done)
             sys_.run(chunk, dt, restart=(done == 0))
             done += chunk
+            if pending:
+                collect()
+                pending = False
             if done % interval == 0:
-                f = sys_.get_frame(0, 16)
-                frames["count"] += 1
-                frames["bytes"] += f.nbytes
+                sys_.frame_begin(0, 16)
+                pending = True
             if on_chunk:
                 on_chunk(done)
+        if pending:
+            collect()
 
     def timed(name, sys_, n_beads, steps, fn):
         sys_.synchronize()
@@ -78,17 +96,20 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     ga.set_seeds([seed + 1])
     n = nsteps(mcfg.telophase_steps)
     timed("telophase", ga, md_ana.n, n, lambda: run_sampled(ga, n, mcfg.timestep, mcfg.sampling_interval))
-    x_telo = ga.get_positions()
-    ga.close()
-
     # ---- relaxation / interphase (SIM/stage_interphase/simulation_driver*.cpp) -----------
+    # transition interphase: spline refinement of the telophase chains, on the device
     t0 = time.perf_counter()
-    x0 = synth.quantize_f32(transitions.transition_interphase(md_ana, design, x_telo)).astype(np.float64)
-    report["transition_interphase_s"] = time.perf_counter() - t0
     gi = System(design.n, 1, device)
     stages.setup_interphase(gi, design, icfg)
     gi.set_seeds([seed + 2])
-    gi.set_positions(x0)
+    if host_transitions:
+        x_telo = synth.quantize_f32(ga.get_positions()).astype(np.float64)
+        x0 = synth.quantize_f32(transitions.transition_interphase(md_ana, design, x_telo)).astype(np.float64)
+        gi.set_positions(x0)
+    else:
+        gi.transition_interphase_from(ga, md_ana.chains, design.chains, design.nucleolar_bonds, bits=16)
+    ga.close()
+    report["transition_interphase_s"] = time.perf_counter() - t0
     stages.begin_relaxation(gi, icfg)
     n = nsteps(icfg.relaxation_steps)
     timed("relaxation", gi, design.n, n,
@@ -109,24 +130,38 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     ctx = gi.get_context()
     report["interphase_end"] = {"time": ctx.time, "semiaxes": list(ctx.semiaxes),
                                 "core_scale": ctx.core_scale}
-    x_inter = gi.get_positions()
-    gi.close()
 
     # ---- prometaphase (SIM/stage_prometaphase/simulation_driver.cpp:185-237) ---------------
+    # transition prometaphase: x100 centroid coarse-graining + displaced sister copy
     t0 = time.perf_counter()
-    xp = synth.quantize_f32(transitions.transition_prometaphase(design, md_pro, mcfg, x_inter))
-    report["transition_prometaphase_s"] = time.perf_counter() - t0
     gp = System(md_pro.n, 1, device)
     stages.setup_prometaphase(gp, md_pro, mcfg)
     gp.set_seeds([seed + 4])
-    gp.set_positions(xp.astype(np.float64))
+    axis = np.asarray(mcfg.spindle_axis, dtype=np.float64)
+    if host_transitions:
+        x_inter = synth.quantize_f32(gi.get_positions()).astype(np.float64)
+        xp = synth.quantize_f32(transitions.transition_prometaphase(design, md_pro, mcfg, x_inter))
+        gp.set_positions(xp.astype(np.float64))
+    else:
+        gp.transition_prometaphase_from(gi, design.chains, md_pro.chains[md_pro.sisters[:, 0]],
+                                        md_pro.chains[md_pro.sisters[:, 1]], mcfg.coarse_graining,
+                                        -mcfg.sister_separation * axis / np.linalg.norm(axis), bits=16)
+    gi.close()
+    report["transition_prometaphase_s"] = time.perf_counter() - t0
     n = nsteps(mcfg.prometaphase_steps)
     timed("prometaphase", gp, md_pro.n, n, lambda: run_sampled(gp, n, mcfg.timestep, mcfg.sampling_interval))
-    x_meta = gp.get_positions()
+    # transition cycle: the target chromatids start the daughter cell's anaphase
+    gn = System(md_ana.n, 1, device)
+    if host_transitions:
+        x_meta = synth.quantize_f32(gp.get_positions()).astype(np.float64)
+        gn.set_positions(synth.quantize_f32(transitions.transition_cycle(md_pro, md_ana, mcfg, x_meta)).astype(np.float64))
+    else:
+        gn.transition_cycle_from(gp, md_pro.chains[md_pro.sisters[:, 0]], md_ana.chains, -axis, bits=16)
     gp.close()
     report["frames_saved"] = frames["count"]
     report["frame_bytes"] = frames["bytes"]
-    report["next_anaphase_start"] = transitions.transition_cycle(md_pro, md_ana, mcfg, x_meta)
+    report["next_anaphase_start"] = gn.get_positions()
+    gn.close()
     total_bs = sum(int(r["beads"]) * int(r["steps"]) for r in report["stages"])
     total_s = sum(r["seconds"] for r in report["stages"])
     report["total_seconds"] = total_s

@@ -53,9 +53,16 @@ def transition_prometaphase(interphase_design, prometaphase_design, mitotic_cfg,
         ts, te = prometaphase_design.chains[t_idx]
         ss, _ = prometaphase_design.chains[s_idx]
         for off in range(te - ts):
-            a = min(s + cg * off, e - 1)
-            b = min(a + cg, e)                 # guard for chains shorter than cg * coarse length
-            centroid = xi[a:b].mean(axis=0)
+            # the reference's window, as written (transition_prometaphase.cpp:87-88):
+            # [start, min(start + cg, start + source_length)).  With prepare's coarse length
+            # floor(len / cg) it never leaves the chain; where a design asks for more coarse
+            # beads than that it runs on into the following chain, exactly as the reference
+            # does.  Only the end of the position array stops it here (the reference would
+            # read out of bounds there; synthetic test designs with >= 3 coarse beads on
+            # very short chains reach that case).
+            a = min(s + cg * off, len(xi) - 1)
+            b = min(a + cg, a + (e - s), len(xi))
+            centroid = xi[a:b].sum(axis=0) / float(b - a)
             x[ts + off] = centroid
             x[ss + off] = centroid + disp
     return x

@@ -308,6 +308,38 @@ int gc_decomp_buffers(gc_ctx *ctx, void **send, void **recv, size_t *elems);
 int gc_decomp_step_compute(gc_ctx *ctx);
 int gc_decomp_step_commit(gc_ctx *ctx);
 
+/* ---- inter-stage transitions on the device ---------------------------------
+   The reference runs `transition {interphase|prometaphase|cycle}` as a separate program
+   between stage binaries, through the trajectory file.  Here the positions move between two
+   contexts of the SAME device without leaving it (a multi-generation lineage stays on the
+   GPU).  Ranges are [n_chains][2] = [start, end) bead indices; arithmetic is FP64 as in the
+   reference; fraction_bits > 0 reproduces the file hand-off (the source is rounded as the
+   stored last frame would be and the result as frame 0 of the next stage,
+   SIM/common/simulation_store.cpp:22-32; the reference uses 16), 0 skips the rounding.
+   Each call returns when the destination positions are written. */
+
+/* telophase -> relaxation (SIM/stage_transition/transition_interphase.cpp:13-84): every
+   coarse chain is fitted with a not-a-knot cubic spline at t = (k + 1/2) / n
+   (cxx-spline) and resampled along its interphase chain at t = (i + 1/2) / m; then
+   dst[copy_pairs[k][1]] = dst[copy_pairs[k][0]] (nucleolar beads start on their NOR bead).
+   Source chains of 3 beads, where the reference's spline is singular, use the parabola. */
+int gc_transition_interphase(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                             int32_t n_chains, const int32_t *src_ranges, const int32_t *dst_ranges,
+                             int32_t n_copies, const int32_t *copy_pairs, int32_t fraction_bits);
+/* interphase -> prometaphase (transition_prometaphase.cpp:24-105): bead k of target chain c =
+   centroid of source beads [s + cg k, min(s + cg k + cg, s + cg k + len_c)), its sister copy
+   = centroid + displacement (-sister_separation along the spindle axis).  sister_ranges may
+   be NULL (coarse-graining only). */
+int gc_transition_prometaphase(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                               int32_t n_chains, const int32_t *src_ranges, const int32_t *target_ranges,
+                               const int32_t *sister_ranges, int32_t coarse_graining,
+                               const double displacement[3], int32_t fraction_bits);
+/* prometaphase -> next anaphase (transition_cycle.cpp:25-76): dst chain = src chain (the
+   target chromatid) + displacement (-spindle_axis). */
+int gc_transition_cycle(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t dst_replica,
+                        int32_t n_chains, const int32_t *src_ranges, const int32_t *dst_ranges,
+                        const double displacement[3], int32_t fraction_bits);
+
 /* ---- observables ------------------------------------------------------- */
 
 /* Squared radius of gyration per chain range [start, end) (harness-defined

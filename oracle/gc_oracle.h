@@ -111,6 +111,23 @@ double gco_bending_probe(double bending_energy, const double rij[3], const doubl
    out = {undefined, delta xyz, strain xyz, implicit} */
 void gco_ellipsoid_probe(const double semiaxes[3], const double pt[3], double out[8]);
 
+/* ---- inter-stage transitions and the stored-frame rounding ----------
+   resample_chain of SIM/stage_transition/transition_interphase.cpp:13-41: not-a-knot cubic
+   spline through the n points of `chain` at t = (k + 1/2) / n, evaluated at
+   t = (i + 1/2) / new_n.  The reference build uses the reference's own
+   submodules/github.com/snsinfu/cxx-spline/include/spline.hpp; the port restates it. */
+void gco_resample_chain(int32_t n, const double *chain, int32_t new_n, double *out);
+/* the centroid loop of SIM/stage_transition/transition_prometaphase.cpp:81-98 for ONE
+   chromosome: coarse_len windows of `cg` beads starting at positions + 3 * source_start
+   (window end = min(start + cg, start + source_len), as written there); writes the target
+   chromatid to target[coarse_len][3] and the sister copy, displaced by disp, to sister. */
+void gco_coarse_grain(const double *positions, int64_t source_start, int64_t source_len,
+                      int64_t cg, int64_t coarse_len, const double disp[3], double *target,
+                      double *sister);
+/* quantize() of SIM/common/simulation_store.cpp:22-32 followed by the f32 store of
+   save_positions (192-216): out[k] = (float) quantize(in[k], bits). */
+void gco_quantize_f32(size_t n, const double *in, int32_t bits, float *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -853,4 +853,112 @@ void gco_ellipsoid_probe(const double semiaxes[3], const double pt[3], double ou
     out[7] = ev.implicit;
 }
 
+
+// ---- inter-stage transitions, restated (no dependency on the reference tree) --------------
+// Not-a-knot cubic spline as submodules/github.com/snsinfu/cxx-spline/include/spline.hpp
+// builds it: second derivatives M from a tridiagonal system (rows 0 and n closed by the
+// not-a-knot conditions, eliminated with row pivoting), piecewise cubics anchored at the left
+// knot, the boundary pieces extended outside the knot range.
+namespace {
+
+struct PortSpline {
+    std::vector<double> knot, c0, c1, c2, c3;
+
+    PortSpline(const std::vector<double> &t, const std::vector<double> &x)
+    {
+        const size_t ns = t.size() - 1;
+        std::vector<double> h(ns), sl(ns);
+        for (size_t i = 0; i < ns; i++) { h[i] = t[i + 1] - t[i]; sl[i] = (x[i + 1] - x[i]) / h[i]; }
+        std::vector<double> L(ns + 1, 0.0), D(ns + 1, 0.0), U(ns + 1, 0.0), Y(ns + 1, 0.0);
+        if (ns == 1) {
+            D[0] = 1; D[ns] = 1;                       // a straight line
+        } else {
+            D[0] = h[0] - h[1]; U[0] = 2 * h[0] + h[1];
+            Y[0] = -6 * h[0] / (h[0] + h[1]) * (sl[0] - sl[1]);
+            D[ns] = h[ns - 1] - h[ns - 2]; L[ns] = 2 * h[ns - 1] + h[ns - 2];
+            Y[ns] = 6 * h[ns - 1] / (h[ns - 1] + h[ns - 2]) * (sl[ns - 1] - sl[ns - 2]);
+        }
+        for (size_t i = 1; i < ns; i++) {
+            L[i] = h[i - 1]; D[i] = 2 * (h[i - 1] + h[i]); U[i] = h[i]; Y[i] = 6 * (sl[i] - sl[i - 1]);
+        }
+        const size_t dim = ns + 1;
+        for (size_t i = 0; i + 1 < dim; i++) {
+            if (std::fabs(D[i]) >= std::fabs(L[i + 1])) {
+                const double w = L[i + 1] / D[i];
+                D[i + 1] -= w * U[i]; Y[i + 1] -= w * Y[i]; L[i + 1] = 0;
+            } else {                                     // row interchange
+                const double w = D[i] / L[i + 1], u = D[i + 1];
+                D[i] = L[i + 1]; D[i + 1] = U[i] - w * u; L[i + 1] = U[i + 1]; U[i + 1] *= -w; U[i] = u;
+                const double r = Y[i];
+                Y[i] = Y[i + 1]; Y[i + 1] = r - w * Y[i + 1];
+            }
+        }
+        Y[dim - 1] /= D[dim - 1];
+        for (size_t rev = 2; rev <= dim; rev++) {
+            const size_t i = dim - rev;
+            if (i == dim - 2) Y[i] -= U[i] * Y[i + 1];
+            else Y[i] -= U[i] * Y[i + 1] + L[i + 1] * Y[i + 2];
+            Y[i] /= D[i];
+        }
+        for (size_t i = 0; i < ns; i++) {
+            knot.push_back(t[i]);
+            c0.push_back(x[i]);
+            c1.push_back(sl[i] - (Y[i + 1] + 2 * Y[i]) * h[i] / 6);
+            c2.push_back(Y[i] / 2);
+            c3.push_back((Y[i + 1] - Y[i]) / (6 * h[i]));
+        }
+        knot.push_back(t[ns]);
+    }
+
+    double operator()(double t) const
+    {
+        const size_t ns = c0.size();
+        size_t i = 0;
+        if (t >= knot[ns]) i = ns - 1;
+        else if (t > knot[0]) { while (i + 1 < ns && t >= knot[i + 1]) i++; }
+        const double d = t - knot[i];
+        return ((c3[i] * d + c2[i]) * d + c1[i]) * d + c0[i];
+    }
+};
+
+} // namespace
+
+void gco_resample_chain(int32_t n, const double *chain, int32_t new_n, double *out)
+{
+    std::vector<double> ts(n), v(n);
+    for (int32_t k = 0; k < n; k++) ts[k] = (0.5 + double(k)) / double(n);
+    for (int c = 0; c < 3; c++) {
+        for (int32_t k = 0; k < n; k++) v[k] = chain[3 * k + c];
+        PortSpline sp(ts, v);
+        for (int32_t i = 0; i < new_n; i++) out[3 * i + c] = sp((0.5 + double(i)) / double(new_n));
+    }
+}
+
+void gco_coarse_grain(const double *positions, int64_t source_start, int64_t source_len, int64_t cg,
+                      int64_t coarse_len, const double disp[3], double *target, double *sister)
+{
+    for (int64_t offset = 0; offset < coarse_len; offset++) {
+        const int64_t start = source_start + cg * offset;
+        const int64_t end = std::min(start + cg, start + source_len);
+        double sum[3] = {0, 0, 0}, count = 0;
+        for (int64_t k = start; k < end; k++) {
+            for (int c = 0; c < 3; c++) sum[c] += positions[3 * k + c];
+            count++;
+        }
+        for (int c = 0; c < 3; c++) {
+            target[3 * offset + c] = sum[c] / count;
+            sister[3 * offset + c] = sum[c] / count + disp[c];
+        }
+    }
+}
+
+void gco_quantize_f32(size_t n, const double *in, int32_t bits, float *out)
+{
+    for (size_t k = 0; k < n; k++) {
+        int e;
+        const double m = std::frexp(in[k], &e);
+        out[k] = (float) std::ldexp(std::nearbyint(std::ldexp(m, bits)), e - bits);
+    }
+}
+
 } // extern "C"

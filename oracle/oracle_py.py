@@ -135,6 +135,9 @@ def load(kind="reference"):
         "gco_potential_probe": (C.c_double, [C.c_int32, C.c_double, C.c_double, C.c_double, dp, dp]),
         "gco_bending_probe": (C.c_double, [C.c_double, dp, dp, dp]),
         "gco_ellipsoid_probe": (None, [dp, dp, dp]),
+        "gco_resample_chain": (None, [C.c_int32, dp, C.c_int32, dp]),
+        "gco_coarse_grain": (None, [dp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, dp, dp, dp]),
+        "gco_quantize_f32": (None, [C.c_size_t, dp, C.c_int32, C.POINTER(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -364,3 +367,29 @@ def ellipsoid_probe(semiaxes, pt, kind="reference"):
     load(kind).gco_ellipsoid_probe(_ptr(a, C.c_double), _ptr(b, C.c_double), _ptr(out, C.c_double))
     return dict(undefined=bool(out[0]), delta=out[1:4].copy(), strain=out[4:7].copy(),
                 implicit=out[7])
+
+
+def resample_chain(chain, new_n, kind="reference"):
+    """resample_chain of transition_interphase.cpp:13-41 (the reference's cxx-spline)."""
+    c = _d(chain).reshape(-1, 3)
+    out = np.empty((int(new_n), 3))
+    load(kind).gco_resample_chain(c.shape[0], _ptr(c, C.c_double), int(new_n), _ptr(out, C.c_double))
+    return out
+
+
+def coarse_grain(positions, source_start, source_len, cg, coarse_len, disp, kind="reference"):
+    """One chromosome of transition_prometaphase.cpp:81-98 -> (target, sister)."""
+    x, d = _d(positions), _d(disp)
+    t, s = np.empty((int(coarse_len), 3)), np.empty((int(coarse_len), 3))
+    load(kind).gco_coarse_grain(_ptr(x, C.c_double), int(source_start), int(source_len), int(cg),
+                                int(coarse_len), _ptr(d, C.c_double), _ptr(t, C.c_double),
+                                _ptr(s, C.c_double))
+    return t, s
+
+
+def quantize_f32(x, bits=16, kind="reference"):
+    """simulation_store.cpp:22-32 + the float store of save_positions."""
+    v = _d(x)
+    out = np.empty(v.shape, dtype=np.float32)
+    load(kind).gco_quantize_f32(v.size, _ptr(v, C.c_double), int(bits), _ptr(out, C.c_float))
+    return out

@@ -33,6 +33,7 @@
 #include "common/particle_data.hpp"
 #include "common/potentials/force_flux_potential.hpp"
 #include "stage_interphase/contact_map.hpp"
+#include <spline.hpp>   // submodules/github.com/snsinfu/cxx-spline/include (reference, unmodified)
 
 #include "gc_oracle.h"
 
@@ -783,6 +784,68 @@ void gco_ellipsoid_probe(const double semiaxes[3], const double pt[3], double ou
     out[1] = ev.delta.x; out[2] = ev.delta.y; out[3] = ev.delta.z;
     out[4] = ev.strain.x; out[5] = ev.strain.y; out[6] = ev.strain.z;
     out[7] = ev.implicit;
+}
+
+
+// ---- inter-stage transitions (SIM/stage_transition/*.cpp cannot be compiled here: they
+// include simulation_store.hpp -> <h5.hpp> -> <hdf5.h>, absent; their bodies are restated
+// around the reference's OWN spline implementation, <spline.hpp>, compiled unmodified) ------
+void gco_resample_chain(int32_t n, const double *chain, int32_t new_n, double *out)
+{
+    // transition_interphase.cpp:16-41
+    constexpr auto spline_bc = cubic_spline::not_a_knot;
+    std::vector<double> ts, xs, ys, zs;
+    for (int32_t k = 0; k < n; k++) {
+        auto const t = (0.5 + double(ts.size())) / double(n);
+        ts.push_back(t);
+        xs.push_back(chain[3 * k]);
+        ys.push_back(chain[3 * k + 1]);
+        zs.push_back(chain[3 * k + 2]);
+    }
+    cubic_spline x_spline(ts, xs, spline_bc);
+    cubic_spline y_spline(ts, ys, spline_bc);
+    cubic_spline z_spline(ts, zs, spline_bc);
+    for (int32_t i = 0; i < new_n; i++) {
+        auto const t = (0.5 + double(i)) / double(new_n);
+        out[3 * i] = x_spline(t);
+        out[3 * i + 1] = y_spline(t);
+        out[3 * i + 2] = z_spline(t);
+    }
+}
+
+void gco_coarse_grain(const double *positions, int64_t source_start, int64_t source_len, int64_t cg,
+                      int64_t coarse_len, const double disp[3], double *target, double *sister)
+{
+    // transition_prometaphase.cpp:24-41 (compute_centroid) and 81-98, with md::point / md::vector
+    md::vector const sister_displacement = {disp[0], disp[1], disp[2]};
+    for (int64_t offset = 0; offset < coarse_len; offset++) {
+        auto const start = source_start + cg * offset;
+        auto const end = std::min(start + cg, start + source_len);
+        md::point const origin = {};
+        md::vector coords = {};
+        md::scalar count = 0;
+        for (int64_t k = start; k < end; k++) {
+            md::point const point = {positions[3 * k], positions[3 * k + 1], positions[3 * k + 2]};
+            coords += point - origin;
+            count++;
+        }
+        coords /= count;
+        md::point const centroid = origin + coords;
+        md::point const sis = centroid + sister_displacement;
+        target[3 * offset] = centroid.x; target[3 * offset + 1] = centroid.y; target[3 * offset + 2] = centroid.z;
+        sister[3 * offset] = sis.x; sister[3 * offset + 1] = sis.y; sister[3 * offset + 2] = sis.z;
+    }
+}
+
+void gco_quantize_f32(size_t n, const double *in, int32_t bits, float *out)
+{
+    // simulation_store.cpp:22-32 (quantize) + 199-207 (the float cast of save_positions)
+    for (size_t k = 0; k < n; k++) {
+        int exp;
+        auto const mant = std::frexp(in[k], &exp);
+        auto const scaled_mant = std::nearbyint(std::ldexp(mant, bits));
+        out[k] = float(std::ldexp(scaled_mant, exp - bits));
+    }
 }
 
 } // extern "C"
