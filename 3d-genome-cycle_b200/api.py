@@ -119,6 +119,22 @@ SYMBOLS = [
     ("gc_transition_interphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, C.c_int32, _ip, C.c_int32]),
     ("gc_transition_prometaphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, _ip, C.c_int32, _dp, C.c_int32]),
     ("gc_transition_cycle", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, _dp, C.c_int32]),
+    ("gc_obs_create", C.c_int, [C.c_int32, C.c_int32, C.c_int32, _ip, C.POINTER(_P)]),
+    ("gc_obs_destroy", C.c_int, [_P]),
+    ("gc_obs_last_error", C.c_char_p, [_P]),
+    ("gc_obs_set_bead_map", C.c_int, [_P, C.c_int32, _ip, _ip]),
+    ("gc_obs_clear", C.c_int, [_P]),
+    ("gc_obs_add_runs_device", C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_size_t]),
+    ("gc_obs_add_triples", C.c_int, [_P, C.POINTER(C.c_uint32), C.c_size_t]),
+    ("gc_obs_get_matrix", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_obs_set_matrix", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_obs_ps_runs_device", C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32, C.POINTER(C.c_uint64)]),
+    ("gc_obs_expected", C.c_int, [_P, _dp, C.c_int32, _dp]),
+    ("gc_obs_max_separation", C.c_int, [_P, _ip]),
+    ("gc_obs_pc1", C.c_int, [_P, C.c_int32, C.c_int32, C.c_double, C.c_int32, C.POINTER(C.c_float),
+                             C.POINTER(C.c_float), _dp, _ip]),
+    ("gc_obs_nci", C.c_int, [_P, C.POINTER(C.c_float)]),
+    ("gc_obs_type_enrichment", C.c_int, [_P, _ip, C.c_int32, C.c_int32, _dp]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
@@ -558,3 +574,93 @@ class System:
         v = C.c_void_p()
         self._ck(self.lib.gc_stream(self._h, C.byref(v)))
         return v.value
+
+
+class Observables:
+    """Binned contact matrix + derived observables on one GPU (thin wrapper over gc_obs)."""
+
+    def __init__(self, n_bins, chrom_ranges, device=0):
+        self.lib = load_library()
+        self.n_bins = int(n_bins)
+        r = _i(chrom_ranges).reshape(-1, 2)
+        self._h = _P()
+        rc = self.lib.gc_obs_create(int(device), self.n_bins, r.shape[0], _ptr(r, C.c_int32), C.byref(self._h))
+        if rc != 0:
+            msg = self.lib.gc_obs_last_error(self._h).decode() if self._h else "no CUDA device"
+            raise GcError(rc, msg)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.gc_obs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise GcError(rc, self.lib.gc_obs_last_error(self._h).decode())
+
+    def set_bead_map(self, bead_bin, bead_chain=None):
+        b = _i(bead_bin)
+        c = _i(bead_chain) if bead_chain is not None else None
+        self._ck(self.lib.gc_obs_set_bead_map(self._h, b.size, _ptr(b, C.c_int32),
+                                              _ptr(c, C.c_int32) if c is not None else None))
+
+    def clear(self):
+        self._ck(self.lib.gc_obs_clear(self._h))
+
+    def add_runs(self, keys, counts):
+        """(keys, counts): CUDA tensors as System.contacts_reduce_device returns them."""
+        keys, counts = keys.contiguous(), counts.contiguous()
+        self._ck(self.lib.gc_obs_add_runs_device(self._h, keys.data_ptr(), counts.data_ptr(), keys.numel()))
+
+    def add_triples(self, ijv):
+        t = np.ascontiguousarray(ijv, dtype=np.uint32).reshape(-1, 3)
+        self._ck(self.lib.gc_obs_add_triples(self._h, _ptr(t, C.c_uint32), t.shape[0]))
+
+    def matrix(self):
+        out = np.empty((self.n_bins, self.n_bins), dtype=np.float32)
+        self._ck(self.lib.gc_obs_get_matrix(self._h, _ptr(out, C.c_float)))
+        return out
+
+    def set_matrix(self, m):
+        x = np.ascontiguousarray(m, dtype=np.float32).reshape(self.n_bins, self.n_bins)
+        self._ck(self.lib.gc_obs_set_matrix(self._h, _ptr(x, C.c_float)))
+
+    def ps_runs(self, keys, counts, max_s):
+        keys, counts = keys.contiguous(), counts.contiguous()
+        hist = np.zeros(int(max_s) + 1, dtype=np.uint64)
+        self._ck(self.lib.gc_obs_ps_runs_device(self._h, keys.data_ptr(), counts.data_ptr(), keys.numel(),
+                                                int(max_s), _ptr(hist, C.c_uint64)))
+        return hist
+
+    def expected(self):
+        n = C.c_int32()
+        self._ck(self.lib.gc_obs_max_separation(self._h, C.byref(n)))
+        intra, inter = np.empty(n.value), C.c_double()
+        self._ck(self.lib.gc_obs_expected(self._h, _ptr(intra, C.c_double), n.value, C.byref(inter)))
+        return intra, inter.value
+
+    def pc1(self, mask_intra=False, use_covariance=False, tolerance=1e-4, max_steps=500):
+        ev1, pc1 = np.empty(self.n_bins, dtype=np.float32), np.empty(self.n_bins, dtype=np.float32)
+        evr, steps = C.c_double(), C.c_int32()
+        self._ck(self.lib.gc_obs_pc1(self._h, int(mask_intra), int(use_covariance), float(tolerance),
+                                     int(max_steps), _ptr(ev1, C.c_float), _ptr(pc1, C.c_float),
+                                     C.byref(evr), C.byref(steps)))
+        return dict(ev1=ev1, pc1=pc1, evr=evr.value, steps=steps.value)
+
+    def nci(self):
+        out = np.empty(self.n_bins, dtype=np.float32)
+        self._ck(self.lib.gc_obs_nci(self._h, _ptr(out, C.c_float)))
+        return out
+
+    def type_enrichment(self, bin_type, n_types, min_separation=0):
+        t = _i(bin_type)
+        out = np.empty((int(n_types), int(n_types)))
+        self._ck(self.lib.gc_obs_type_enrichment(self._h, _ptr(t, C.c_int32), int(n_types), int(min_separation),
+                                                 _ptr(out, C.c_double)))
+        return out

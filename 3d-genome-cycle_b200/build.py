@@ -8,7 +8,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
 LIB = PKG_DIR / "libgc_b200.so"
-SOURCES = ["gc_api.cu"]
+SOURCES = ["gc_api.cu", "gc_obs.cu"]
 HEADERS = ["gc_types.cuh", "gc_math.cuh", "gc_kernels.cuh", "gc_pairwalk.cuh", "gc_step.cuh", "gc_query.cuh", "gc_tile.cuh", "gc_cells.cuh", "gc_contact.cuh", "gc_decomp.cuh", "gc_transition.cuh", "gc_peak.cuh"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -17,7 +17,7 @@ import time
 
 import numpy as np
 
-from . import stages, synth, transitions
+from . import prepare, stages, synth, transitions
 from .api import System
 
 
@@ -37,6 +37,10 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
               "stages": []}
 
     frames = {"count": 0, "bytes": 0}
+    # the 64-bit seed of every simulate call, derived from the master seed exactly as the
+    # reference derives them (prepare.py: std::seed_seq -> per-stage mt19937_64)
+    seeds = prepare.run_seeds(seed)
+    report["seeds"] = {k: int(v) for k, v in seeds.items()}
 
     def run_sampled(sys_, n, dt, interval, on_chunk=None):
         """n steps in chunks of the sampling interval; after each chunk the driver's
@@ -71,6 +75,8 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
             collect()
 
     def timed(name, sys_, n_beads, steps, fn):
+        if frame_sink is not None and hasattr(frame_sink, "begin_stage"):
+            frame_sink.begin_stage(name)
         sys_.synchronize()
         t0 = time.perf_counter()
         fn()
@@ -87,13 +93,13 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     # ---- anaphase / telophase (SIM/stage_anatelophase/simulation_driver.cpp:192-310) ----
     ga = System(md_ana.n, 1, device)
     ta = stages.setup_anatelophase(ga, md_ana, mcfg)
-    ga.set_seeds([seed])
+    ga.set_seeds([seeds["anaphase"]])
     ga.set_positions(synth.rod_positions(md_ana, mcfg, seed=seed))
     stages.enter_anaphase(ga, ta)
     n = nsteps(mcfg.anaphase_steps)
     timed("anaphase", ga, md_ana.n, n, lambda: run_sampled(ga, n, mcfg.timestep, mcfg.sampling_interval))
     stages.enter_telophase(ga, ta)
-    ga.set_seeds([seed + 1])
+    ga.set_seeds([seeds["telophase"]])
     n = nsteps(mcfg.telophase_steps)
     timed("telophase", ga, md_ana.n, n, lambda: run_sampled(ga, n, mcfg.timestep, mcfg.sampling_interval))
     # ---- relaxation / interphase (SIM/stage_interphase/simulation_driver*.cpp) -----------
@@ -101,7 +107,7 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     t0 = time.perf_counter()
     gi = System(design.n, 1, device)
     stages.setup_interphase(gi, design, icfg)
-    gi.set_seeds([seed + 2])
+    gi.set_seeds([seeds["relaxation"]])
     if host_transitions:
         x_telo = synth.quantize_f32(ga.get_positions()).astype(np.float64)
         x0 = synth.quantize_f32(transitions.transition_interphase(md_ana, design, x_telo)).astype(np.float64)
@@ -115,7 +121,7 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     timed("relaxation", gi, design.n, n,
           lambda: gi.run(n, icfg.timestep, spacestep=icfg.relaxation_spacestep))
     stages.begin_interphase(gi, icfg)
-    gi.set_seeds([seed + 3])
+    gi.set_seeds([seeds["interphase"]])
     n = nsteps(icfg.steps)
     window = icfg.sampling_interval * icfg.contactmap_output_window
 
@@ -136,7 +142,7 @@ def run_cell_cycle(design=None, icfg=None, mcfg=None, seed=1, device=0, scale_st
     t0 = time.perf_counter()
     gp = System(md_pro.n, 1, device)
     stages.setup_prometaphase(gp, md_pro, mcfg)
-    gp.set_seeds([seed + 4])
+    gp.set_seeds([seeds["prometaphase"]])
     axis = np.asarray(mcfg.spindle_axis, dtype=np.float64)
     if host_transitions:
         x_inter = synth.quantize_f32(gi.get_positions()).astype(np.float64)

@@ -31,6 +31,16 @@ def replica_seeds(master_seed: int, cell_ids) -> np.ndarray:
     return np.asarray(out, dtype=np.uint64)
 
 
+def replica_seeds_reference(master_base: int, cell_ids, stage: str = "interphase") -> np.ndarray:
+    """Seeds as a reference ensemble derives them: cell c is `scripts/simulate -s (master_base +
+    c)`, whose `prepare` turns the master seed into per-stage seeds with std::seed_seq and whose
+    stage driver draws the seed of every simulate call from std::mt19937_64(stage seed)
+    (prepare.py: run_seeds; SIM/stage_prepare/prepare.cpp:549-562).  The value returned for a
+    cell is the one the reference hands md::simulate_brownian_dynamics for `stage`."""
+    from .prepare import run_seeds
+    return np.asarray([run_seeds(int(master_base) + int(c))[stage] for c in cell_ids], dtype=np.uint64)
+
+
 def merge_contacts_torch(keys, counts):
     """Reference merge (plain torch, any device): sort + sum of equal keys."""
     import torch

@@ -352,6 +352,51 @@ int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
    need_rebuild, parity, dt_cur, 0, 0, 0}. */
 int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16]);
 
+/* ---- contact-map observables on the device (gc_obs.cu) ----------------------
+   The reference computes these offline in Python from the trajectory file; here the ensemble
+   contact map is already on the GPU as sorted (key, count) runs, so the binned matrix and
+   everything derived from it are built there.  One gc_obs = one n_bins x n_bins float32 matrix
+   on one device.  chrom_ranges = [n_chroms][2] bin ranges [start, end), ascending. */
+typedef struct gc_obs gc_obs;
+int gc_obs_create(int32_t device, int32_t n_bins, int32_t n_chroms, const int32_t *chrom_ranges,
+                  gc_obs **out);
+int gc_obs_destroy(gc_obs *obs);
+const char *gc_obs_last_error(const gc_obs *obs);
+/* bead -> bin (< 0 drops the bead) and, optionally, bead -> chain (for gc_obs_ps_runs_device). */
+int gc_obs_set_bead_map(gc_obs *obs, int32_t n_beads, const int32_t *bead_bin, const int32_t *bead_chain);
+int gc_obs_clear(gc_obs *obs);
+/* Adds contact pixels to the symmetric bin matrix as cooler's matrix() shows the pixels that
+   src/cool.py:80-110 ingests (mirrored, the diagonal counted once): DEVICE runs as returned by
+   gc_contacts_reduce_device / gc_contacts_merge_device, or host (i, j, count) triples. */
+int gc_obs_add_runs_device(gc_obs *obs, const uint64_t *keys, const uint32_t *counts, size_t n);
+int gc_obs_add_triples(gc_obs *obs, const uint32_t *ijv, size_t n);
+int gc_obs_get_matrix(gc_obs *obs, float *out);          /* [n_bins][n_bins] */
+int gc_obs_set_matrix(gc_obs *obs, const float *in);
+/* P(s) at bead resolution straight from device runs: hist[s] = sum of counts of intra-chain
+   pairs with j - i = s, s = 0..max_s (hist = [max_s + 1], host). */
+int gc_obs_ps_runs_device(gc_obs *obs, const uint64_t *keys, const uint32_t *counts, size_t n,
+                          int32_t max_s, uint64_t *hist);
+/* estimate_expected_contacts (src/pc1.py:156-183): intra[s] = mean finite contact on the s-th
+   diagonal over all chromosomes (the cis decay profile), inter = mean finite trans contact.
+   capacity = length of intra (gc_obs_max_separation gives the longest chromosome). */
+int gc_obs_expected(gc_obs *obs, double *intra, int32_t capacity, double *inter);
+int gc_obs_max_separation(gc_obs *obs, int32_t *out);
+/* src/pc1.py:36-101 + src/pkg/pc1/math.py:13-37: O/E transform, column selection (coverage >
+   0) and standardisation, first right singular vector by power iteration until max |dv| <
+   tolerance, PC1 = data @ v scaled so that var(PC1) is the explained variance ratio.
+   ev1 / pc1 = [n_bins] (ev1 NaN on dropped bins). */
+int gc_obs_pc1(gc_obs *obs, int32_t mask_intra, int32_t use_covariance, double tolerance,
+               int32_t max_steps, float *ev1, float *pc1, double *explained_variance_ratio,
+               int32_t *steps);
+/* compute_nci (src/pkg/nci/nci.py:9-35): out[i] = M[i][i+1] / sqrt(M[i][i] M[i+1][i+1]) inside a
+   chromosome, NaN on every chromosome's last bin; out = [n_bins]. */
+int gc_obs_nci(gc_obs *obs, float *out);
+/* Compartment strength (harness-defined): mean finite contact between bins of type
+   a and b (bin_type in [0, n_types), < 0 ignores the bin) over pairs i < j that are trans or
+   at least min_separation apart; mean_contact = [n_types][n_types], symmetric. */
+int gc_obs_type_enrichment(gc_obs *obs, const int32_t *bin_type, int32_t n_types,
+                           int32_t min_separation, double *mean_contact);
+
 /* ---- measurement (bench.py; no reference counterpart) ------------------- */
 
 /* Per-kernel CUDA-event timing on the context's stream.  While enabled every
