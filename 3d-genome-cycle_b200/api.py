@@ -136,6 +136,7 @@ SYMBOLS = [
     ("gc_obs_nci", C.c_int, [_P, C.POINTER(C.c_float)]),
     ("gc_obs_type_enrichment", C.c_int, [_P, _ip, C.c_int32, C.c_int32, _dp]),
     ("gc_radius_of_gyration", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
+    ("gc_radius_of_gyration_noalloc", C.c_int, [_P, C.c_int32, C.c_int32, _ip, _dp]),
     ("gc_debug_grid", C.c_int, [_P, C.c_int32, _dp]),
     ("gc_profile_enable", C.c_int, [_P, C.c_int32]),
     ("gc_profile_read", C.c_int, [_P, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), _dp]),
@@ -537,6 +538,14 @@ class System:
         out = np.empty(r.shape[0], dtype=np.float64)
         self._ck(self.lib.gc_radius_of_gyration(self._h, replica, r.shape[0], _ptr(r, C.c_int32),
                                                 _ptr(out, C.c_double)))
+        return out
+
+    def radius_of_gyration2_noalloc(self, ranges, replica=0):
+        """gc_radius_of_gyration_noalloc: static device scratch, at most 4096 ranges."""
+        r = _i(ranges).reshape(-1, 2)
+        out = np.empty(r.shape[0], dtype=np.float64)
+        self._ck(self.lib.gc_radius_of_gyration_noalloc(self._h, replica, r.shape[0], _ptr(r, C.c_int32),
+                                                        _ptr(out, C.c_double)))
         return out
 
     def debug_grid(self, replica=0):

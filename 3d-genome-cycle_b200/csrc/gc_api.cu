@@ -1815,6 +1815,75 @@ int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges, const 
     return GC_OK;
 }
 
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of gc_radius_of_gyration
+// (no counterpart in the reference).  The scratch of k_rg2 -- the chain ranges and
+// the per-chain results -- lives in a file-scope device array instead of cudaMalloc'ed
+// buffers: 64 KiB held by every GPU that loads the library, until exit.  In host code the
+// array's NAME is only a host-side stand-in; the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------
+struct RgScratch {
+    int ranges[2 * GC_RG_NOALLOC_MAX_RANGES];
+    double out[GC_RG_NOALLOC_MAX_RANGES];
+};
+static __device__ __align__(256) RgScratch g_rg_scratch;
+
+namespace {
+constexpr int RG_MAX_DEVICES = 64;
+RgScratch *g_rg_scratch_ptr[RG_MAX_DEVICES] = {};
+
+// device address of g_rg_scratch on ctx's device (which GC_CHECK_CTX has made current)
+int rg_scratch_address(gc_ctx *ctx, RgScratch **out)
+{
+    if (ctx->device < 0 || ctx->device >= RG_MAX_DEVICES) return fail(ctx, GC_ERR_INVALID, "device index %d", ctx->device);
+    if (!g_rg_scratch_ptr[ctx->device]) {
+        void *p = nullptr;
+        GC_CUDA(ctx, cudaGetSymbolAddress(&p, g_rg_scratch));
+        g_rg_scratch_ptr[ctx->device] = static_cast<RgScratch *>(p);
+    }
+    *out = g_rg_scratch_ptr[ctx->device];
+    return GC_OK;
+}
+} // namespace
+
+extern "C" {
+
+int gc_radius_of_gyration_noalloc(gc_ctx *ctx, int32_t replica, int32_t n_ranges, const int32_t *ranges,
+                                  double *out_rg2)
+{
+    GC_CHECK_CTX(ctx);
+    if (replica < 0 || replica >= ctx->n_rep || n_ranges < 0 || (n_ranges && (!ranges || !out_rg2))) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    if (n_ranges > GC_RG_NOALLOC_MAX_RANGES) {
+        return fail(ctx, GC_ERR_CAPACITY, "gc_radius_of_gyration_noalloc: %d ranges exceed the static scratch of %d "
+                    "(use gc_radius_of_gyration)", n_ranges, GC_RG_NOALLOC_MAX_RANGES);
+    }
+    if (n_ranges == 0) return GC_OK;
+    for (int g = 0; g < n_ranges; g++) {
+        if (ranges[2 * g] < 0 || ranges[2 * g + 1] > ctx->n || ranges[2 * g] > ranges[2 * g + 1]) {
+            return fail(ctx, GC_ERR_INVALID, "bad range %d", g);
+        }
+    }
+    RgScratch *scratch = nullptr;
+    int rc = rg_scratch_address(ctx, &scratch);
+    if (rc) return rc;
+    // the array keeps the last call's contents: the results this call reads back start at 0
+    GC_CUDA(ctx, cudaMemsetAsync(scratch->out, 0, (size_t) n_ranges * sizeof(double), ctx->stream));
+    GC_CUDA(ctx, cudaMemcpyAsync(scratch->ranges, ranges, (size_t) 2 * n_ranges * sizeof(int),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    k_rg2<<<n_ranges, 256, 0, ctx->stream>>>(ctx->hp, replica, n_ranges, scratch->ranges, scratch->out);
+    ctx->launches++;
+    GC_CUDA(ctx, cudaGetLastError());
+    GC_CUDA(ctx, cudaMemcpyAsync(out_rg2, scratch->out, (size_t) n_ranges * sizeof(double),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GC_OK;
+}
+
 int gc_debug_grid(gc_ctx *ctx, int32_t replica, double out[16])
 {
     GC_CHECK_CTX(ctx);

@@ -347,6 +347,18 @@ int gc_transition_cycle(gc_ctx *src, int32_t src_replica, gc_ctx *dst, int32_t d
 int gc_radius_of_gyration(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
                           const int32_t *ranges, double *out_rg2);
 
+/* The same WITHOUT any allocation, for callers that cannot call cudaMalloc (code under CUDA
+   graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the
+   reference.  The kernel's scratch (the ranges
+   and the per-range results) lives in a static device array of the library, so n_ranges is
+   limited to GC_RG_NOALLOC_MAX_RANGES (4096; 64 KiB per GPU that loads the library, held until
+   exit); more returns GC_ERR_CAPACITY.  Calls no cudaMalloc / cudaFree and does not touch the
+   context's topology.  All contexts and calls on one GPU share the array: calls that overlap
+   on the GPU (different contexts / streams / host threads) race -- serialise them. */
+#define GC_RG_NOALLOC_MAX_RANGES 4096
+int gc_radius_of_gyration_noalloc(gc_ctx *ctx, int32_t replica, int32_t n_ranges,
+                                  const int32_t *ranges, double *out_rg2);
+
 /* Diagnostic view of the cell list of one replica: out = {dims x,y,z, ncell,
    origin x,y,z, cell_size, rc_valid, max displacement since rebuild,
    need_rebuild, parity, dt_cur, 0, 0, 0}. */
