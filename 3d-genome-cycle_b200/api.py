@@ -112,8 +112,10 @@ SYMBOLS = [
                                            C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                            C.POINTER(C.c_size_t)]),
     ("gc_decomp_configure", C.c_int, [_P, C.c_int32, C.c_int32]),
-    ("gc_decomp_buffers", C.c_int, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
-                                    C.POINTER(C.c_size_t)]),
+    ("gc_decomp_set_halo", C.c_int, [_P, C.c_int32, C.c_int32]),
+    ("gc_decomp_buffers", C.c_int, [_P] + [C.POINTER(C.c_void_p)] * 6 + [C.POINTER(C.c_size_t)]),
+    ("gc_decomp_step_pack", C.c_int, [_P]),
+    ("gc_decomp_owned", C.c_int, [_P, C.c_void_p]),
     ("gc_decomp_step_compute", C.c_int, [_P]),
     ("gc_decomp_step_commit", C.c_int, [_P]),
     ("gc_transition_interphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, C.c_int32, _ip, C.c_int32]),
@@ -485,17 +487,34 @@ class System:
         self._decomp_world = int(world)
         self._ck(self.lib.gc_decomp_configure(self._h, int(rank), int(world)))
 
+    def decomp_set_halo(self, layers, capacity=0):
+        self._ck(self.lib.gc_decomp_set_halo(self._h, int(layers), int(capacity)))
+
     def decomp_buffers(self, device=0):
-        """(send, recv) as flat float32 CUDA tensors viewing the context's buffers:
-        send = [elems * 4], recv = [world * elems * 4]."""
+        """dict of flat CUDA tensors viewing the context's exchange buffers: send_lo, send_hi,
+        recv_lo, recv_hi (float32 [halo_elems * 4]) and header [16], headers_all [world * 16]
+        (float64)."""
         import torch
-        a, b, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
-        self._ck(self.lib.gc_decomp_buffers(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        p = [C.c_void_p() for _ in range(6)]
+        n = C.c_size_t()
+        self._ck(self.lib.gc_decomp_buffers(self._h, *[C.byref(x) for x in p], C.byref(n)))
         dev = torch.device("cuda", device)
-        send = torch.as_tensor(_DeviceArray(a.value, n.value * 4, "<f4"), device=dev)
-        world = self._decomp_world
-        recv = torch.as_tensor(_DeviceArray(b.value, world * n.value * 4, "<f4"), device=dev)
-        return send, recv
+        out = {}
+        for name, x in zip(("send_lo", "send_hi", "recv_lo", "recv_hi"), p[:4]):
+            out[name] = torch.as_tensor(_DeviceArray(x.value, n.value * 4, "<f4"), device=dev)
+        out["header"] = torch.as_tensor(_DeviceArray(p[4].value, 16, "<f8"), device=dev)
+        out["headers_all"] = torch.as_tensor(_DeviceArray(p[5].value, 16 * self._decomp_world, "<f8"),
+                                             device=dev)
+        return out
+
+    def decomp_step_pack(self):
+        self._ck(self.lib.gc_decomp_step_pack(self._h))
+
+    def decomp_owned(self):
+        """bool [n]: the beads this rank owns now."""
+        m = np.zeros(self.n, dtype=np.uint8)
+        self._ck(self.lib.gc_decomp_owned(self._h, m.ctypes.data))
+        return m.astype(bool)
 
     def decomp_step_compute(self):
         self._ck(self.lib.gc_decomp_step_compute(self._h))

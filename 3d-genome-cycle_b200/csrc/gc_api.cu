@@ -316,7 +316,8 @@ int gc_create(int32_t n_beads, int32_t n_replicas, int32_t device, gc_ctx **out)
     if (!rc) rc = dev_alloc(ctx, &P.sref, RN);
     if (!rc) rc = dev_alloc(ctx, &P.scell, RN);
     if (!rc) rc = dev_alloc(ctx, &P.sab, RN);
-    P.n_units = (n_beads + 1) / 2 + 1;
+    P.max_layers = std::min(1024, std::max(64, n_beads / 4));
+    P.n_units = (n_beads + 1) / 2 + 1 + P.max_layers;
     P.unit_plane = (size_t) n_replicas * (size_t) P.n_units;
     if (!rc) rc = dev_alloc(ctx, &P.punit, 3 * P.unit_plane);
     if (!rc) rc = dev_alloc(ctx, &P.members, RN);
@@ -932,6 +933,16 @@ int check_device_errors(gc_ctx *ctx)
             return fail(ctx, GC_ERR_CAPACITY, "replica %d: contact table full (capacity %llu)", r,
                         (unsigned long long) ctx->hp.contact.capacity);
         }
+        if (st[r].error == 3) {
+            return fail(ctx, GC_ERR_STATE, "decomposed run, step %lld: a bonded partner or a moved bead lies "
+                        "outside the %d-layer halo, or a slab is thinner than the halo "
+                        "(gc_decomp_set_halo, or fewer ranks)", st[r].step, ctx->hp.dhalo);
+        }
+        if (st[r].error == 4) {
+            return fail(ctx, GC_ERR_CAPACITY, "decomposed run, step %lld: halo buffer full (%d beads; "
+                        "gc_decomp_set_halo) or the ranks' bead counts do not add up", st[r].step,
+                        ctx->hp.dcap);
+        }
     }
     return GC_OK;
 }
@@ -1178,6 +1189,13 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
     if (c->restart) {
         LAUNCH(ctx, k_restart, (ctx->n_rep + 63) / 64, 64, ctx->hp, c->timestep);
         ctx->run_step = 0;
+    }
+    if (P.decomp) {
+        // restart: every rank holds all N positions (gc_set_positions), all are current.
+        // Otherwise only the parameters were refreshed: the grid of the last step stands,
+        // and a bounding box over this rank's partly stale positions would be wrong.
+        if (!c->restart) return GC_OK;
+        LAUNCH(ctx, k_decomp_stamp_all, (ctx->n + 255) / 256, 256, ctx->hp);
     }
     plan_and_rebuild(ctx, 0.0);
 
@@ -1957,43 +1975,110 @@ int gc_launch_count(gc_ctx *ctx, int64_t *out)
 // ---------------------------------------------------------------------------
 // spatial decomposition (gc_decomp.cuh)
 // ---------------------------------------------------------------------------
+namespace {
+
+void decomp_release(gc_ctx *ctx)
+{
+    Params &P = ctx->hp;
+    if (P.dstamp) dev_free(ctx, P.dstamp);
+    if (P.dsend_lo) dev_free(ctx, P.dsend_lo);
+    if (P.dsend_hi) dev_free(ctx, P.dsend_hi);
+    if (P.drecv_lo) dev_free(ctx, const_cast<float4 *>(P.drecv_lo));
+    if (P.drecv_hi) dev_free(ctx, const_cast<float4 *>(P.drecv_hi));
+    if (P.dhdr) dev_free(ctx, P.dhdr);
+    if (P.dhdr_all) dev_free(ctx, const_cast<double *>(P.dhdr_all));
+    P.dstamp = nullptr;
+    P.dsend_lo = P.dsend_hi = nullptr;
+    P.drecv_lo = P.drecv_hi = nullptr;
+    P.dhdr = nullptr;
+    P.dhdr_all = nullptr;
+    P.decomp = 0;
+    ctx->params_dirty = true;
+}
+
+int decomp_alloc_halo(gc_ctx *ctx, int cap)
+{
+    Params &P = ctx->hp;
+    float4 *b[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int k = 0; k < 4; k++) {
+        int rc = dev_alloc(ctx, &b[k], (size_t) cap + 1);
+        if (rc) return rc;
+        GC_CUDA(ctx, cudaMemsetAsync(b[k], 0, ((size_t) cap + 1) * sizeof(float4), ctx->stream));
+    }
+    if (P.dsend_lo) dev_free(ctx, P.dsend_lo);
+    if (P.dsend_hi) dev_free(ctx, P.dsend_hi);
+    if (P.drecv_lo) dev_free(ctx, const_cast<float4 *>(P.drecv_lo));
+    if (P.drecv_hi) dev_free(ctx, const_cast<float4 *>(P.drecv_hi));
+    P.dsend_lo = b[0];
+    P.dsend_hi = b[1];
+    P.drecv_lo = b[2];
+    P.drecv_hi = b[3];
+    P.dcap = cap;
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+} // namespace
+
 int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world)
 {
     GC_CHECK_CTX(ctx);
     if (world < 1 || rank < 0 || rank >= world) return fail(ctx, GC_ERR_INVALID, "bad rank / world");
     if (ctx->n_rep != 1) return fail(ctx, GC_ERR_STATE, "decomposition needs n_replicas = 1");
-    Params &P = ctx->hp;
-    if (P.dsend) dev_free(ctx, P.dsend);
-    if (P.drecv) dev_free(ctx, const_cast<float4 *>(P.drecv));
-    P.dsend = nullptr;
-    P.drecv = nullptr;
-    P.decomp = 0;
-    ctx->params_dirty = true;
+    decomp_release(ctx);
     if (world == 1) return GC_OK;
-    const int chunk = (ctx->n + world - 1) / world;
-    float4 *send = nullptr, *recv = nullptr;
-    int rc = dev_alloc(ctx, &send, (size_t) chunk + 2);
-    if (!rc) rc = dev_alloc(ctx, &recv, (size_t) world * ((size_t) chunk + 2));
+    Params &P = ctx->hp;
+    int *stamp = nullptr;
+    double *hdr = nullptr, *hdr_all = nullptr;
+    int rc = dev_alloc(ctx, &stamp, (size_t) ctx->n);
+    if (!rc) rc = dev_alloc(ctx, &hdr, (size_t) DHDR);
+    if (!rc) rc = dev_alloc(ctx, &hdr_all, (size_t) DHDR * world);
     if (rc) return rc;
-    GC_CUDA(ctx, cudaMemsetAsync(send, 0, ((size_t) chunk + 2) * sizeof(float4), ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(stamp, 0, (size_t) ctx->n * sizeof(int), ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(hdr, 0, DHDR * sizeof(double), ctx->stream));
+    GC_CUDA(ctx, cudaMemsetAsync(hdr_all, 0, (size_t) DHDR * world * sizeof(double), ctx->stream));
+    P.dstamp = stamp;
+    P.dhdr = hdr;
+    P.dhdr_all = hdr_all;
+    // a rank never ships more than it owns; an equal-volume slab of a uniformly filled
+    // nucleus owns about N / world beads, 2x that is a generous default
+    rc = decomp_alloc_halo(ctx, std::max(1024, (int) std::min<long long>(ctx->n, 2LL * ((ctx->n + world - 1) / world))));
+    if (rc) return rc;
     P.decomp = 1;
+    P.drank = rank;
     P.dworld = world;
-    P.dchunk = chunk;
-    P.own_lo = std::min(rank * chunk, ctx->n);
-    P.own_hi = std::min(P.own_lo + chunk, ctx->n);
-    P.dsend = send;
-    P.drecv = recv;
+    P.dhalo = std::max(2, P.cells_per_cut);
     return GC_OK;
 }
 
-int gc_decomp_buffers(gc_ctx *ctx, void **send, void **recv, size_t *elems)
+int gc_decomp_set_halo(gc_ctx *ctx, int32_t layers, int32_t capacity)
 {
     GC_CHECK_CTX(ctx);
-    if (!send || !recv || !elems) return fail(ctx, GC_ERR_INVALID, "bad args");
-    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
-    *send = ctx->hp.dsend;
-    *recv = const_cast<float4 *>(ctx->hp.drecv);
-    *elems = (size_t) ctx->hp.dchunk + 2;
+    Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    if (layers < 1 || capacity < 0) return fail(ctx, GC_ERR_INVALID, "bad halo layers / capacity");
+    P.dhalo = layers;
+    ctx->params_dirty = true;
+    if (capacity > 0 && capacity != P.dcap) return decomp_alloc_halo(ctx, capacity);
+    return GC_OK;
+}
+
+int gc_decomp_buffers(gc_ctx *ctx, void **send_lo, void **send_hi, void **recv_lo, void **recv_hi,
+                      void **header, void **headers_all, size_t *halo_elems)
+{
+    GC_CHECK_CTX(ctx);
+    if (!send_lo || !send_hi || !recv_lo || !recv_hi || !header || !headers_all || !halo_elems) {
+        return fail(ctx, GC_ERR_INVALID, "bad args");
+    }
+    const Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    *send_lo = P.dsend_lo;
+    *send_hi = P.dsend_hi;
+    *recv_lo = const_cast<float4 *>(P.drecv_lo);
+    *recv_hi = const_cast<float4 *>(P.drecv_hi);
+    *header = P.dhdr;
+    *headers_all = const_cast<double *>(P.dhdr_all);
+    *halo_elems = (size_t) P.dcap + 1;
     return GC_OK;
 }
 
@@ -2008,9 +2093,20 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
     launch_pair(ctx, 0u, 1);
-    const int owned = P.own_hi - P.own_lo;
-    LAUNCH(ctx, k_finish<STEP_FUSED>, dim3(std::max((owned + BS - 1) / BS, 1), 1), BS, ctx->hp, 0u, 1);
+    LAUNCH(ctx, k_finish<STEP_FUSED>, dim3((ctx->n + BS - 1) / BS, 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);
+    return GC_OK;
+}
+
+int gc_decomp_step_pack(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    LAUNCH(ctx, k_decomp_reduce, 1, 32, ctx->hp);
+    LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
+    LAUNCH(ctx, k_decomp_pack, (ctx->n + 255) / 256, 256, ctx->hp);
+    ctx->run_step++;
+    ctx->parity ^= 1;
     return GC_OK;
 }
 
@@ -2018,11 +2114,25 @@ int gc_decomp_step_commit(gc_ctx *ctx)
 {
     GC_CHECK_CTX(ctx);
     if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
-    LAUNCH(ctx, k_decomp_scatter, std::min((ctx->n + 255) / 256, 148 * 8), 256, ctx->hp);
-    LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
-    ctx->run_step++;
-    ctx->parity ^= 1;
+    const int blocks = std::max(1, std::min((ctx->hp.dcap + 255) / 256, 148 * 4));
+    LAUNCH(ctx, k_decomp_unpack, dim3(blocks, 2), 256, ctx->hp);
     return GC_OK;
+}
+
+int gc_decomp_owned(gc_ctx *ctx, uint8_t *mask)
+{
+    GC_CHECK_CTX(ctx);
+    if (!mask) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    unsigned char *d = nullptr;
+    int rc = dev_alloc(ctx, &d, (size_t) ctx->n);
+    if (rc) return rc;
+    k_decomp_owned<<<(ctx->n + 255) / 256, 256, 0, ctx->stream>>>(ctx->hp, d);
+    cudaError_t e = cudaMemcpyAsync(mask, d, (size_t) ctx->n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    dev_free(ctx, d);
+    if (e != cudaSuccess) return fail(ctx, GC_ERR_CUDA, cudaGetErrorString(e));
+    return check_device_errors(ctx);
 }
 
 // ---------------------------------------------------------------------------

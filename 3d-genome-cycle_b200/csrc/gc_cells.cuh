@@ -250,11 +250,16 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
         if (TICKET == 2) cellB = __ldg(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
         int loA = 0, u1A = 0, loB = 0, u1B = 0;
         if (lane < 9) {
-            loA = __ldg(&start[cellA.x + row_rel]);
-            u1A = (__ldg(&start[cellA.x + row_rel + 3]) + 1) >> 1;
+            // slots -> the layer-relative unit space of the pair-interleaved copy (unit_slot)
+            const int LA = cellA.w + lane / 3 - 1;
+            const int sA = unit_slot(0, LA, __ldg(&start[LA * dxy]));
+            loA = __ldg(&start[cellA.x + row_rel]) + sA;
+            u1A = (__ldg(&start[cellA.x + row_rel + 3]) + sA + 1) >> 1;
             if (TICKET == 2) {
-                loB = __ldg(&start[cellB.x + row_rel]);
-                u1B = (__ldg(&start[cellB.x + row_rel + 3]) + 1) >> 1;
+                const int LB = cellB.w + lane / 3 - 1;
+                const int sB = unit_slot(0, LB, __ldg(&start[LB * dxy]));
+                loB = __ldg(&start[cellB.x + row_rel]) + sB;
+                u1B = (__ldg(&start[cellB.x + row_rel + 3]) + sB + 1) >> 1;
             }
         }
         int h0 = cellA.y, nhome = cellA.z, lo = loA, u1 = u1A;

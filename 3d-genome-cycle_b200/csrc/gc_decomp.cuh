@@ -1,92 +1,164 @@
 // gc_decomp.cuh -- one large replica spread over several GPUs (BASELINE configs[4],
 // SURVEY.md 8e row 2; not in the reference, which is single-process).
 //
-// Decomposition by SORTED SLOT RANGE.  Every rank holds all N positions and builds the
-// same cell list (x-fastest, z-slowest, so a contiguous slot range is a z-slab of the
-// nucleus with ragged edges).  Rank k evaluates the nonbonded forces of the cells that
-// hold slots [k C, (k + 1) C), C = ceil(N / ranks), and moves exactly those beads
-// (k_gather filters the work queue, k_finish the slots).  The new positions leave in
-// slot order as (x, y, z, bead) in Params::dsend, followed by a 32-byte header with this
-// rank's share of the wall reaction sums; ONE all-gather (NCCL over NVLink) puts every
-// rank's buffer into Params::drecv, and k_decomp_scatter below writes all N beads back
-// by bead index, rebuilds the bounding box and sums the headers in rank order.  Every
-// bead's force is a gather over its full neighbourhood and the noise is keyed by (seed,
-// bead, step), so the trajectory is bit-identical to the single-GPU one whatever the
-// number of ranks (tests/test_decomp.py).
+// SLAB + HALO decomposition.  The cell grid is x-fastest / z-slowest, so a range of z
+// layers is a contiguous range of cells AND of sorted slots.  Rank k owns the layers
+// [slab_start(k), slab_start(k + 1)) of the global grid (equal-volume slabs of the
+// bounding ellipsoid) and bins only the beads whose position is CURRENT on it: its own
+// beads plus the halo copies its two neighbours sent after the previous step.  Every bead
+// carries the step at which this rank last wrote it (Params::dstamp); a bead that left
+// the halo simply stops being current and drops out of the cell list.
+//
+// One step on rank k:
+//   gc_decomp_step_compute   cell list over the window [z0 - 1, z1 + 1), pair forces of the
+//                            owned layers, k_finish moves the owned beads (new position in
+//                            pos[], stamp = step + 1), k_decomp_header writes the rank's
+//                            share of the per-step reductions (bounding box, wall sums,
+//                            error) to a 128-byte header
+//   all-gather of the headers (world x 128 bytes; NCCL)
+//   gc_decomp_step_pack      k_decomp_reduce folds the headers in rank order, the per-step
+//                            callback body plans the NEXT grid (identical on every rank);
+//                            k_decomp_pack appends each moved bead whose new layer lies
+//                            within dhalo layers of the neighbour's new slab -- or inside
+//                            it: ownership follows the position -- to the send buffer of
+//                            that neighbour, as (x, y, z, bead)
+//   send/recv with rank - 1 and rank + 1 (NCCL point-to-point over NVLink)
+//   gc_decomp_step_commit    k_decomp_unpack writes the received beads by bead index and
+//                            stamps them current
+//
+// The exchange is O(surface): 2 neighbours x (beads in dhalo + 1 layers) x 16 bytes instead
+// of round 1's all-gather of all N beads to every rank.  Every bead's force is still a
+// gather over its complete neighbourhood, evaluated in the order of the same cell list
+// arithmetic, and the noise is keyed by (seed, bead, step, epoch): the trajectory is
+// bit-identical to the single-GPU one whatever the number of ranks (tests/test_decomp.py).
 #pragma once
 
 #include "gc_step.cuh"
 
 namespace gc {
 
-// after k_finish: this rank's partial wall statistics -> header of the send buffer
+constexpr int DHDR = 16;     // doubles per rank header
+
+// after k_finish: this rank's share of the per-step reductions
 __global__ void k_decomp_header(const __grid_constant__ Params P)
 {
     GC_PDL_ENTRY();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     RepState &st = P.st[0];
-    long long *h = reinterpret_cast<long long *>(P.dsend + P.dchunk);
-    h[0] = st.axial_fx[0];
-    h[1] = st.axial_fx[1];
-    h[2] = st.axial_fx[2];
-    h[3] = st.reaction_fx;
+    double *h = P.dhdr;
+    long long *hl = reinterpret_cast<long long *>(h);
+    int *hi = reinterpret_cast<int *>(h + 4);
+    hl[0] = st.axial_fx[0];
+    hl[1] = st.axial_fx[1];
+    hl[2] = st.axial_fx[2];
+    hl[3] = st.reaction_fx;
+    for (int k = 0; k < 3; k++) { hi[k] = st.bbox_min[k]; hi[3 + k] = st.bbox_max[k]; }
+    hi[6] = st.error;
+    // beads moved by this rank (diagnostics: the counts of all ranks must add up to N)
+    const int *start = P.cell_start;
+    const int dxy = st.dims[0] * st.dims[1];
+    hi[7] = start[st.zown_hi * dxy] - start[st.zown_lo * dxy];
+    // the send buffers restart empty
+    reinterpret_cast<int *>(P.dsend_lo)[0] = 0;
+    reinterpret_cast<int *>(P.dsend_hi)[0] = 0;
 }
 
-// after the all-gather: every bead's new position by bead index, bounding box of all
-// beads (the next grid plan), wall statistics summed over ranks in rank order
-__global__ void __launch_bounds__(256) k_decomp_scatter(const __grid_constant__ Params P)
+// after the header all-gather: the reductions of the whole system, folded in rank order
+// (integer sums and min/max: order-independent anyway), then the per-step callback body
+__global__ void k_decomp_reduce(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    RepState &st = P.st[0];
+    long long sum[4] = {0, 0, 0, 0};
+    int bmin[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+    int bmax[3] = {(int) 0x80000000, (int) 0x80000000, (int) 0x80000000};
+    int err = 0, moved = 0;
+    for (int k = 0; k < P.dworld; k++) {
+        const double *h = P.dhdr_all + (size_t) k * DHDR;
+        const long long *hl = reinterpret_cast<const long long *>(h);
+        const int *hi = reinterpret_cast<const int *>(h + 4);
+        for (int c = 0; c < 4; c++) sum[c] += hl[c];
+        for (int c = 0; c < 3; c++) { bmin[c] = min(bmin[c], hi[c]); bmax[c] = max(bmax[c], hi[3 + c]); }
+        if (!err) err = hi[6];
+        moved += hi[7];
+    }
+    for (int c = 0; c < 3; c++) { st.axial_fx[c] = sum[c]; st.bbox_min[c] = bmin[c]; st.bbox_max[c] = bmax[c]; }
+    st.reaction_fx = sum[3];
+    if (!err && moved != P.n) err = 4;           // a bead was lost or moved twice
+    if (err) st.error = err;
+}
+
+// after the callback body planned the next grid: ship the moved beads the neighbours need
+__global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Params P)
 {
     GC_PDL_ENTRY();
     RepState &st = P.st[0];
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    bool bad = false;
-    float4 *__restrict__ out = P.pos[st.parity ^ 1];
-    for (int t = blockIdx.x * 256 + threadIdx.x; t < P.n; t += gridDim.x * 256) {      // slot
-        const int k = t / P.dchunk;
-        const float4 v = P.drecv[(size_t) k * (P.dchunk + 2) + (t - k * P.dchunk)];
-        out[__float_as_int(v.w)] = make_float4(v.x, v.y, v.z, 0.0f);
-        lo[0] = fminf(lo[0], v.x); hi[0] = fmaxf(hi[0], v.x);
-        lo[1] = fminf(lo[1], v.y); hi[1] = fmaxf(hi[1], v.y);
-        lo[2] = fminf(lo[2], v.z); hi[2] = fmaxf(hi[2], v.z);
-        bad |= !(fabsf(v.x) < INFINITY && fabsf(v.y) < INFINITY && fabsf(v.z) < INFINITY);
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P.n) return;
+    // moved by this rank in the step just taken (halo copies keep the previous stamp)
+    if (P.dstamp[idx] != (int) st.step) return;
+    const float4 x = P.pos[st.parity][idx];
+    const int h = P.cells_per_cut;
+    const int layer = cell_layer(st, x.z, h);
+    const int z0 = slab_start(P.drank, P.dworld, st.gdimz, h);
+    const int z1 = slab_start(P.drank + 1, P.dworld, st.gdimz, h);
+    // a bead that jumped past a neighbour's whole slab would be lost
+    if (layer < slab_start(P.drank - 1, P.dworld, st.gdimz, h) ||
+        layer >= slab_start(P.drank + 2, P.dworld, st.gdimz, h)) {
+        atomicExch(&st.error, 3);
     }
-    // block reduction, then 6 atomics per block
-    __shared__ float sh[8][6];
-    __shared__ int sh_bad;
-    if (threadIdx.x == 0) sh_bad = 0;
-    for (int k = 0; k < 3; k++) {
-        for (int o = 16; o > 0; o >>= 1) {
-            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
-            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
-        }
+    const float4 v = make_float4(x.x, x.y, x.z, __int_as_float(idx));
+    if (P.drank > 0 && layer < z0 + P.dhalo) {
+        const int k = atomicAdd(reinterpret_cast<int *>(P.dsend_lo), 1);
+        if (k < P.dcap) P.dsend_lo[1 + k] = v; else atomicExch(&st.error, 4);
     }
-    __syncthreads();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) {
-        for (int k = 0; k < 3; k++) { sh[wid][k] = lo[k]; sh[wid][3 + k] = hi[k]; }
+    if (P.drank + 1 < P.dworld && layer >= z1 - P.dhalo) {
+        const int k = atomicAdd(reinterpret_cast<int *>(P.dsend_hi), 1);
+        if (k < P.dcap) P.dsend_hi[1 + k] = v; else atomicExch(&st.error, 4);
     }
-    if (bad) sh_bad = 1;
-    __syncthreads();
-    if (threadIdx.x < 3) {
-        float l = sh[0][threadIdx.x], h = sh[0][3 + threadIdx.x];
-        for (int w = 1; w < 8; w++) { l = fminf(l, sh[w][threadIdx.x]); h = fmaxf(h, sh[w][3 + threadIdx.x]); }
-        if (l <= h) {
-            atomicMin(&st.bbox_min[threadIdx.x], float_to_ordered(l));
-            atomicMax(&st.bbox_max[threadIdx.x], float_to_ordered(h));
-        }
+}
+
+// after the neighbour exchange: received beads by bead index, stamped current
+__global__ void __launch_bounds__(256) k_decomp_unpack(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    RepState &st = P.st[0];
+    float4 *__restrict__ pos = P.pos[st.parity];
+    const int side = blockIdx.y;
+    if (side == 0 && P.drank == 0) return;
+    if (side == 1 && P.drank + 1 >= P.dworld) return;
+    const float4 *buf = side == 0 ? P.drecv_lo : P.drecv_hi;
+    const int count = min(reinterpret_cast<const int *>(buf)[0], P.dcap);
+    for (int k = blockIdx.x * 256 + threadIdx.x; k < count; k += gridDim.x * 256) {
+        const float4 v = buf[1 + k];
+        const int idx = __float_as_int(v.w);
+        pos[idx] = make_float4(v.x, v.y, v.z, 0.0f);
+        P.dstamp[idx] = (int) st.step;
     }
-    if (threadIdx.x == 0 && sh_bad) atomicExch(&st.error, 1);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        long long sum[4] = {0, 0, 0, 0};
-        for (int k = 0; k < P.dworld; k++) {
-            const long long *h = reinterpret_cast<const long long *>(P.drecv + (size_t) k * (P.dchunk + 2) + P.dchunk);
-            for (int c = 0; c < 4; c++) sum[c] += h[c];
-        }
-        st.axial_fx[0] = sum[0];
-        st.axial_fx[1] = sum[1];
-        st.axial_fx[2] = sum[2];
-        st.reaction_fx = sum[3];
+}
+
+// gc_run(steps = 0, restart = 1): every rank was handed all N positions
+__global__ void __launch_bounds__(256) k_decomp_stamp_all(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < P.n) P.dstamp[i] = (int) P.st[0].step;
+}
+
+// mask of the beads this rank owns now (position current and inside its slab)
+__global__ void __launch_bounds__(256) k_decomp_owned(const __grid_constant__ Params P, unsigned char *mask)
+{
+    RepState &st = P.st[0];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P.n) return;
+    unsigned char own = 0;
+    if (P.dstamp[i] == (int) st.step) {
+        const int layer = cell_layer(st, P.pos[st.parity][i].z, P.cells_per_cut);
+        own = layer >= slab_start(P.drank, P.dworld, st.gdimz, P.cells_per_cut) &&
+              layer < slab_start(P.drank + 1, P.dworld, st.gdimz, P.cells_per_cut);
     }
+    mask[i] = own;
 }
 
 } // namespace gc

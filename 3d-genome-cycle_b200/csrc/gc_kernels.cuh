@@ -69,12 +69,51 @@ __device__ __forceinline__ int cell_coord(float x, float origin, float inv, int 
     return min(max(c, halo), dim - 1 - halo);
 }
 
+// z layer of a position in the GLOBAL grid (identical arithmetic on every rank of a
+// decomposed run)
+__device__ __forceinline__ int cell_layer(const RepState &st, float z, int halo)
+{
+    return cell_coord(z, st.origin[2], st.inv_cell, st.gdimz, halo);
+}
+
+// Cell of a position, or -1 when its layer lies outside this context's z-window (a decomposed
+// run bins only its slab plus one layer on either side; otherwise the window is the grid).
 __device__ __forceinline__ int cell_index(const RepState &st, float4 p, int halo)
 {
     int cx = cell_coord(p.x, st.origin[0], st.inv_cell, st.dims[0], halo);
     int cy = cell_coord(p.y, st.origin[1], st.inv_cell, st.dims[1], halo);
-    int cz = cell_coord(p.z, st.origin[2], st.inv_cell, st.dims[2], halo);
+    int cz = cell_layer(st, p.z, halo) - st.zoff;
+    if (cz < 0 || cz >= st.dims[2]) return -1;
     return cx + st.dims[0] * (cy + st.dims[1] * cz);
+}
+
+// First layer of rank k's slab in a grid of gdimz layers, the outer `halo` layers on either
+// side being the always-empty margin: slabs of EQUAL VOLUME of the ellipsoid the bounding box
+// encloses -- the volume fraction of an ellipsoid below height u in [-1, 1] is
+// (2 + 3u - u^3) / 4, inverted in closed form -- so that the ranks of a roughly uniformly
+// filled nucleus own similar bead counts.
+__device__ __host__ inline int slab_start(int k, int world, int gdimz, int halo)
+{
+    const int nint = gdimz - 2 * halo;
+    if (k <= 0) return halo;
+    if (k >= world) return halo + nint;
+    const double f = (double) k / (double) world;
+    const double u = 2.0 * cos((acos(1.0 - 2.0 * f) + 4.0 * 3.14159265358979323846) / 3.0);
+    const int z = halo + (int) floor(0.5 * (u + 1.0) * (double) nint + 0.5);
+    return z < halo ? halo : (z > halo + nint ? halo + nint : z);
+}
+
+// z-window of this rank: its slab plus the pair halo (cells_per_cut layers) on either side
+__device__ inline void decomp_window(const Params &P, RepState &st)
+{
+    const int h = P.cells_per_cut;
+    const int z0 = slab_start(P.drank, P.dworld, st.gdimz, h), z1 = slab_start(P.drank + 1, P.dworld, st.gdimz, h);
+    // a slab thinner than the position halo would need beads from beyond the neighbouring rank
+    if (z1 - z0 < P.dhalo) st.error = 3;
+    st.zoff = z0 - h;
+    st.dims[2] = (z1 - z0) + 2 * h;
+    st.zown_lo = h;
+    st.zown_hi = h + (z1 - z0);
 }
 
 // Chooses origin / cell size / dims from the bounding box for list radius
@@ -108,14 +147,19 @@ __device__ inline void plan_grid(const Params &P, RepState &st, double rlist)
             dims[k] = (int) d;
             tot *= d;
         }
-        if (tot <= (double) P.ncell_max) break;
+        if (tot <= (double) P.ncell_max && dims[2] <= P.max_layers) break;
         cs *= 1.2599210498948732;   // 2^(1/3): halves the cell count per round
     }
     for (int k = 0; k < 3; k++) {
         st.dims[k] = dims[k];
         st.origin[k] = (float) ((double) lo[k] - cs * P.cells_per_cut);
     }
-    st.ncell = dims[0] * dims[1] * dims[2];
+    st.gdimz = dims[2];
+    st.zoff = 0;
+    st.zown_lo = 0;
+    st.zown_hi = dims[2];
+    if (P.decomp) decomp_window(P, st);          // dims[2] becomes this rank's layer count
+    st.ncell = st.dims[0] * st.dims[1] * st.dims[2];
     st.cell_size = (float) cs;
     st.inv_cell = (float) (1.0 / cs);
     // A pair is guaranteed to be seen while (distance now) + 2 max displacement
@@ -196,10 +240,14 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
     if (i < P.scan_blocks) P.scan_status[(size_t) r * P.scan_blocks + i] = 0ull;
     if (i == 0) { P.st[r].scan_ticket = 0; P.st[r].n_used_cells = 0; P.st[r].n_light_cells = 0; }
     if (i >= P.n) return;
-    float4 p = P.pos[st.parity][(size_t) r * P.n + i];
-    int c = cell_index(st, p, P.cells_per_cut);
+    int c = -1;
+    // a decomposed run bins the beads whose position is current on this rank
+    if (!P.decomp || P.dstamp[i] == (int) st.step) {
+        float4 p = P.pos[st.parity][(size_t) r * P.n + i];
+        c = cell_index(st, p, P.cells_per_cut);
+    }
     P.cell_of[(size_t) r * P.n + i] = c;
-    atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
+    if (c >= 0) atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
 }
 
 // Exclusive scan of the cell counts: chained multi-block scan with decoupled
@@ -314,6 +362,7 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
     int c = P.cell_of[(size_t) r * P.n + i];
+    if (c < 0) return;
     int s = P.cell_start[(size_t) r * (P.ncell_max + 1) + c] +
             atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
     P.members[(size_t) r * P.n + s] = i;
@@ -325,6 +374,8 @@ __device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r
 {
     size_t ro = (size_t) r * P.n;
     const int *members = P.members + ro;
+    const int total = P.cell_start[(size_t) r * (P.ncell_max + 1) + st.ncell];   // beads binned
+    if (s >= total) return;
     int idx = members[s];
     int c = P.cell_of[ro + idx];
     const int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
@@ -334,12 +385,13 @@ __device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r
     if (rank == 0) {
         P.cell_count[(size_t) r * P.ncell_max + c] = 0;   // cursor back to 0
         // work queue of the pair kernel; its order is arbitrary but no result depends on it
-        // (a decomposed run only evaluates the cells that hold slots of this rank)
-        if (!P.decomp || (base < P.own_hi && end > P.own_lo)) {
+        // (a decomposed run only evaluates the cells of the layers this rank owns)
+        const int layer = c / (st.dims[0] * st.dims[1]);
+        if (!P.decomp || (layer >= st.zown_lo && layer < st.zown_hi)) {
             // well populated cells are queued from the front, the rest from the back:
             // the pair kernel then starts on the heavy ones and fills its tail with
             // light ones (longest-processing-time-first)
-            const int4 item = make_int4(c, base, end - base, 0);
+            const int4 item = make_int4(c, base, end - base, layer);
             if (end - base >= GC_HEAVY_CELL) {
                 P.cell_list[ro + atomicAdd(&st.n_used_cells, 1)] = item;
             } else {
@@ -356,25 +408,27 @@ __device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r
     const float2 ab = P.ab[idx];
     P.sab[ro + dst] = ab;
     {
-        // pair-interleaved copy (k_pair_cells stages whole units)
-        float *u0 = unit_half(P, r, dst, 0), *u1 = unit_half(P, r, dst, 1);
+        // pair-interleaved copy (k_pair_cells stages whole units), paired per layer
+        const int dxy = st.dims[0] * st.dims[1];
+        const int L = c / dxy;
+        const int lstart = start[L * dxy], lend = start[(L + 1) * dxy];
+        const int us = unit_slot(dst, L, lstart);
+        float *u0 = unit_half(P, r, us, 0), *u1 = unit_half(P, r, us, 1);
         u0[0] = p.x;
         u0[2] = p.y;
         u1[0] = p.z;
         u1[2] = ab.x;
-        unit_half(P, r, dst, 2)[0] = ab.y;
-        if (dst == P.n - 1) {
-            // the unused half of the last unit and the pad unit: a dummy bead 64 cells off
-            // the grid with zero mixing factors (finite r^2, force exactly 0)
-            const float fx = st.origin[0] - 64.0f * st.cell_size;
-            for (int t = P.n; t < 2 * P.n_units; t++) {
-                float *d0 = unit_half(P, r, t, 0), *d1 = unit_half(P, r, t, 1);
-                d0[0] = fx;
-                d0[2] = st.origin[1];
-                d1[0] = st.origin[2];
-                d1[2] = 0.0f;
-                unit_half(P, r, t, 2)[0] = 0.0f;
-            }
+        unit_half(P, r, us, 2)[0] = ab.y;
+        if (dst == lend - 1) {
+            // the half behind the last bead of a layer (it shares a unit with that bead when
+            // the layer holds an odd number): a dummy bead 64 cells off the grid with zero
+            // mixing factors (finite r^2, force exactly 0)
+            float *d0 = unit_half(P, r, us + 1, 0), *d1 = unit_half(P, r, us + 1, 1);
+            d0[0] = st.origin[0] - 64.0f * st.cell_size;
+            d0[2] = st.origin[1];
+            d1[0] = st.origin[2];
+            d1[2] = 0.0f;
+            unit_half(P, r, us + 1, 2)[0] = 0.0f;
         }
     }
 }

@@ -96,6 +96,7 @@ __device__ inline void refresh_consts(const Params &P, RepState &st)
 // ---------------------------------------------------------------------------
 struct WallAcc {
     float ax, ay, az, reaction;
+    int stale;            // decomposed run: a bonded partner was not current on this rank
 };
 
 // Single-bead terms only: the nonbonded soft cores come from k_pair_cells.
@@ -120,6 +121,10 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
             const BondTerm &bt = P.bonds[be.bterm];
             if (!(mask >> bt.term & 1u)) continue;
             float4 q = pos[be.partner];
+            // decomposed run: the partner's position must be current here, i.e. lie within
+            // the position halo (Params::dhalo layers) of this rank's slab.  (Stamps of beads
+            // this kernel has already moved read step + 1: current is >= step.)
+            if (P.decomp && P.dstamp[be.partner] < (int) st.step) wacc.stale = 1;
             f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
             float K = sc.bK_a[be.bterm], l = sc.bl_a[be.bterm];
             if (bt.mix_ab) {
@@ -142,6 +147,8 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
             TripleEntry te = P.triple_ent[e];
             int tt = te.role_term >> 2, role = te.role_term & 3;
             if (!(mask >> P.triples[tt].term & 1u)) continue;
+            if (P.decomp && (P.dstamp[te.i] < (int) st.step || P.dstamp[te.j] < (int) st.step ||
+                             P.dstamp[te.k] < (int) st.step)) wacc.stale = 1;
             f3 pi = make_f3(pos[te.i]), pj = make_f3(pos[te.j]), pk = make_f3(pos[te.k]);
             f3 f = bending_force(sc.tE[tt], pi - pj, pj - pk, role);
             F = F + f;
@@ -166,6 +173,13 @@ __device__ __forceinline__ f3 bead_force(const Params &P, const RepState &st, in
         for (int k = 0; k < P.well.n_targets; k++) {
             int j = P.well.targets[k];
             if (j == idx) continue;
+            if (P.decomp && P.dstamp[j] < (int) st.step) {
+                // not current here: further than the position halo from this rank's slab,
+                // where the well must have ended (its term is exactly 0 beyond the cutoff)
+                const float reach = (float) P.dhalo * st.cell_size;
+                if (sc.well_cut2 > reach * reach) wacc.stale = 1;
+                continue;
+            }
             float4 q = pos[j];
             f3 d = {self.x - q.x, self.y - q.y, self.z - q.z};
             float fac = well_force_factor(sc.well_eps, sc.well_k2, sc.well_cut2, dot(d, d));
@@ -261,7 +275,7 @@ __device__ __forceinline__ void red_init(StepRed &s)
     for (int k = 0; k < 3; k++) { s.lo[k] = INFINITY; s.hi[k] = -INFINITY; }
     s.disp2 = 0.0f;
     s.dtmin = INFINITY;
-    s.w = {0.0f, 0.0f, 0.0f, 0.0f};
+    s.w = {0.0f, 0.0f, 0.0f, 0.0f, 0};
     s.bad = false;
 }
 
@@ -301,6 +315,7 @@ __device__ __forceinline__ void block_reduce_commit(RepState &st, StepRed &s, bo
         q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
     }
     bool bad = __any_sync(0xffffffffu, s.bad);
+    if (__any_sync(0xffffffffu, s.w.stale != 0) && lane == 0) atomicExch(&st.error, 3);
     __syncthreads();
     if (lane == 0) {
         for (int k = 0; k < 8; k++) sh_i[wid][k] = v[k];
@@ -451,17 +466,20 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
     x.z = self4.z + fmaf(mudt, F.z, 0.5f * (W.z + Wp.z));
     x.w = 0.0f;
     P.pos[par ^ 1][ro + idx] = x;
-    if (P.decomp) P.dsend[t - P.own_lo] = make_float4(x.x, x.y, x.z, self4.w);   // halo exchange payload
+    if (P.decomp) P.dstamp[idx] = (int) n;          // current on this rank for step n (k_decomp_pack ships it)
     if (P.skin > 0.0f) {
         // cells may be reused: keep the sorted copy current and track the largest
         // displacement since the rebuild (neighbor_list.hpp:129-158)
         x.w = self4.w;
         P.spos[par ^ 1][ro + t] = x;
         {   // ... and the pair-interleaved copy the pair kernel stages from
-            float *u0 = unit_half(P, r, t, 0);
+            const int dxy = st.dims[0] * st.dims[1];
+            const int L = P.scell[ro + t] / dxy;
+            const int us = unit_slot(t, L, P.cell_start[(size_t) r * (P.ncell_max + 1) + L * dxy]);
+            float *u0 = unit_half(P, r, us, 0);
             u0[0] = x.x;
             u0[2] = x.y;
-            unit_half(P, r, t, 1)[0] = x.z;
+            unit_half(P, r, us, 1)[0] = x.z;
         }
         float4 ref = P.sref[ro + t];
         float ex = x.x - ref.x, ey = x.y - ref.y, ez = x.z - ref.z;

@@ -3,8 +3,8 @@
 // One thread per sorted slot, full occupancy: bonded pairs and triples, tethers,
 // nucleolar droplet, point sources, wall (+ its reaction statistics), Philox
 // noise and the BAOAB-limit update; consumes the nonbonded force k_pair_cells
-// left in P.pforce.  The last block of a replica runs the per-step callback
-// body (finalize_step).
+// left in P.pforce.  The per-step callback body runs in k_finalize_step, the
+// launch behind this one.
 #pragma once
 
 #include "gc_step.cuh"
@@ -12,7 +12,7 @@
 namespace gc {
 
 // Single-bead terms + update (or force output), one thread per sorted slot, full
-// occupancy; consumes the nonbonded force of k_pair_tile.
+// occupancy; consumes the nonbonded force of k_pair_cells.
 template<int MODE>
 __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P, unsigned mask_arg, int use_enabled)
 {
@@ -20,12 +20,20 @@ __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P,
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    // a decomposed run launches only the blocks of the owned slot range
-    const int t = (P.decomp ? P.own_lo : 0) + blockIdx.x * BS + threadIdx.x;
+    // a decomposed run moves the sorted slots of the layers it owns (contiguous: z is the
+    // slowest cell axis); the grid covers all N slots, the other threads have nothing to do
+    const int t = blockIdx.x * BS + threadIdx.x;
+    int t_lo = 0, t_hi = P.n;
+    if (P.decomp) {
+        const int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
+        const int dxy = st.dims[0] * st.dims[1];
+        t_lo = start[st.zown_lo * dxy];
+        t_hi = start[st.zown_hi * dxy];
+    }
     StepRed red;
     red_init(red);
 
-    if (t < (P.decomp ? P.own_hi : P.n)) {
+    if (t >= t_lo && t < t_hi) {
         const size_t ro = (size_t) r * P.n;
         const float4 self4 = P.spos[st.parity][ro + t];
         const int idx = __float_as_int(self4.w);

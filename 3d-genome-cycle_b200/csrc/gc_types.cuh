@@ -169,6 +169,9 @@ struct RepState {
     int n_light_cells;             // lightly populated cells, queued from the BACK of cell_list
     int contact_cursor;            // work-queue head of k_contact_cells
     int epoch;                     // logical runs since the seeds were set (Philox counter word 3)
+    // z-window of a decomposed run: dims[2] counts the LOCAL layers [zoff, zoff + dims[2]) of the
+    // global grid (gdimz layers); the local layers [zown_lo, zown_hi) are owned by this rank
+    int zoff, gdimz, zown_lo, zown_hi;
     StepConst sc;
 };
 
@@ -205,7 +208,8 @@ struct Params {
     // (x0 x1 y0 y1), (z0 z1 a0 a1), (b0 b1 - -); plane k starts at punit + k * unit_plane
     float4 *punit;
     size_t unit_plane;
-    int n_units;                   // (n + 1) / 2 + 1 (one trailing pad unit)
+    int n_units;                   // (n + 1) / 2 + 1 + max_layers (layer-relative pairing: unit_slot)
+    int max_layers;                // bound on the z layers of the cell grid (plan_grid coarsens beyond)
     int *cell_count, *cell_start, *members, *cell_of;
     unsigned long long *scan_status;   // [R][scan_blocks] look-back words of k_scan
     int scan_blocks;               // ceil(ncell_max / SCAN_TILE)
@@ -213,13 +217,17 @@ struct Params {
     float4 *force;                 // total force, ORIGINAL order (adaptive stepper, gc_compute_force)
     float4 *pforce;                // nonbonded force, SORTED order (k_pair_cells -> k_finish)
     RepState *st;
-    // spatial decomposition of ONE large replica over several GPUs (gc_decomp.cuh):
-    // this rank evaluates and moves the sorted slots [own_lo, own_hi)
+    // spatial decomposition of ONE large replica over several GPUs (gc_decomp.cuh): z-slabs of
+    // the cell grid with a halo exchange between neighbouring ranks
     int decomp;                    // 0: off
-    int own_lo, own_hi;
-    int dworld, dchunk;            // ranks, slots per rank (= ceil(N / ranks))
-    float4 *dsend;                 // [dchunk + 2]: new (x, y, z, bead) of the owned slots + header
-    const float4 *drecv;           // [dworld][dchunk + 2]: every rank's dsend, gathered
+    int drank, dworld;             // this rank, ranks
+    int dhalo;                     // position halo in cell layers (>= 1; bonded partners must lie inside)
+    int dcap;                      // beads per halo buffer
+    int *dstamp;                   // [N] step at which pos[] of a bead was last written on this rank
+    float4 *dsend_lo, *dsend_hi;   // [dcap + 1] (x, y, z, bead) for rank - 1 / rank + 1; [0].x = count bits
+    const float4 *drecv_lo, *drecv_hi;   // the same, received from rank - 1 / rank + 1
+    double *dhdr;                  // [16] this rank's share of the per-step reductions
+    const double *dhdr_all;        // [dworld][16] every rank's header, gathered
     const float *noise;            // injected normals [R][steps][N][3] or null
     long long noise_steps;         // steps covered by `noise`
     long long noise_step0;         // st->step value that maps to noise row 0
@@ -243,6 +251,18 @@ __device__ __forceinline__ float *unit_half(const Params &P, int r, int slot, in
 {
     return reinterpret_cast<float *>(P.punit + (size_t) plane * P.unit_plane + (size_t) r * P.n_units +
                                      (size_t) (slot >> 1)) + (slot & 1);
+}
+
+// Position of sorted slot s (a bead of z layer L, whose first slot is layer_start) in the
+// pair-interleaved copy.  Beads are paired RELATIVE TO THEIR LAYER -- the first bead of a
+// layer always opens a unit -- so the units the pair kernel stages for a home cell, and with
+// them the order of every force sum, depend on the three layers around the cell only: a
+// decomposed run, which bins a window of layers, reproduces the whole-grid sums bit for bit.
+// Layer L occupies units from (layer_start >> 1) + L, which leaves 1-3 unused halves between
+// consecutive layers; the first of them is kept a dummy (gather_slot).
+__device__ __forceinline__ int unit_slot(int s, int L, int layer_start)
+{
+    return s + 2 * L - (layer_start & 1);
 }
 
 static_assert(sizeof(Params) <= 4000, "Params is passed by value as a kernel argument");

@@ -1,58 +1,140 @@
 """One large polymer spread over several GPUs (BASELINE configs[4]): host side of the
-slot-range decomposition in csrc/gc_decomp.cuh.  One process per GPU (torchrun); every
-rank holds all beads, evaluates and moves its slab, and ONE NCCL all-gather per step
-exchanges the new positions.  `LocalExchange` emulates the collective between several
-contexts on one device (tests on a single GPU)."""
+slab + halo decomposition in csrc/gc_decomp.cuh.  One process per GPU (torchrun); every
+rank owns a z-slab of the cell grid and keeps current copies of the beads within a few
+cell layers of it.  Per step: one all-gather of 128-byte headers (global bounding box,
+wall sums, error flag) and one send/recv of halo beads with each of the two neighbouring
+ranks -- surface traffic, not the whole system.  `LocalExchange` emulates the exchange
+between several contexts on one device (tests on a single GPU)."""
 from __future__ import annotations
 
+import numpy as np
 
-def slot_ranges(n_beads: int, world: int):
-    """[lo, hi) of sorted cell-list slots owned by each rank (gc_decomp_configure)."""
-    chunk = (n_beads + world - 1) // world
-    return [(min(r * chunk, n_beads), min(r * chunk + chunk, n_beads)) for r in range(world)]
+HEADER_DOUBLES = 16
+
+
+def slab_starts(world: int, layers: int, margin: int = 1):
+    """First grid layer of every rank's slab plus the end of the last one (mirror of
+    slab_start in csrc/gc_kernels.cuh): equal-volume cuts of the ellipsoid inscribed in the
+    `layers - 2 margin` interior layers.  The volume fraction of an ellipsoid below height
+    u in [-1, 1] is (2 + 3u - u^3) / 4; u(f) = 2 cos((acos(1 - 2f) + 4 pi) / 3) inverts it."""
+    nint = layers - 2 * margin
+    out = []
+    for k in range(world + 1):
+        if k <= 0:
+            out.append(margin)
+        elif k >= world:
+            out.append(margin + nint)
+        else:
+            f = k / world
+            u = 2.0 * np.cos((np.arccos(1.0 - 2.0 * f) + 4.0 * np.pi) / 3.0)
+            z = margin + int(np.floor(0.5 * (u + 1.0) * nint + 0.5))
+            out.append(min(max(z, margin), margin + nint))
+    return out
 
 
 class DecomposedRun:
-    """Drives gc_decomp_step_compute -> all-gather -> gc_decomp_step_commit."""
+    """Drives gc_decomp_step_compute -> header all-gather -> gc_decomp_step_pack ->
+    neighbour send/recv -> gc_decomp_step_commit on the context's own stream."""
 
-    def __init__(self, system, rank: int, world: int, device: int = 0, group=None):
+    scheme = "z-slabs of the cell grid + halo exchange with the two neighbouring ranks"
+
+    def __init__(self, system, rank: int, world: int, device: int = 0, group=None,
+                 halo_layers: int | None = None, halo_capacity: int = 0):
         import torch
         self.sys, self.rank, self.world, self.group = system, rank, world, group
+        self.device = device
         system.decomp_configure(rank, world)
-        self.send = self.recv = None
+        self.buf = None
         if world > 1:
-            self.send, self.recv = system.decomp_buffers(device)
+            if halo_layers is not None or halo_capacity:
+                system.decomp_set_halo(halo_layers or 2, halo_capacity)
+            self.buf = system.decomp_buffers(device)
         self.stream = torch.cuda.ExternalStream(system.stream(), device=device)
 
     def begin(self, timestep, temperature=1.0):
-        """Temperature / timestep, restart, first grid plan (gc_run with 0 steps)."""
+        """Temperature / timestep, restart, first grid plan (gc_run with 0 steps); every rank
+        must have been given all N positions."""
         self.sys.run(0, timestep, temperature=temperature, restart=True)
+
+    @property
+    def exchange_bytes_per_step(self):
+        """Bytes this rank sends per step: its header to every rank plus the two halo buffers
+        (whole buffers travel; the bead count rides in their first element)."""
+        if self.world == 1:
+            return 0
+        halo = self.buf["send_lo"].numel() * 4
+        sides = (self.rank > 0) + (self.rank + 1 < self.world)
+        return HEADER_DOUBLES * 8 * (self.world - 1) + sides * halo
+
+    def halo_counts(self):
+        """(beads sent down, beads sent up) in the last step."""
+        lo = int(self.buf["send_lo"][:1].view(dtype=_i32()).item())
+        hi = int(self.buf["send_hi"][:1].view(dtype=_i32()).item())
+        return lo, hi
 
     def step(self, steps=1):
         import torch
         import torch.distributed as dist
-        s = self.sys
+        s, b = self.sys, self.buf
         if self.world == 1:
             raise RuntimeError("world = 1: use System.run")
+        ops_template = []
+        if self.rank + 1 < self.world:
+            ops_template += [(dist.isend, b["send_hi"], self.rank + 1), (dist.irecv, b["recv_hi"], self.rank + 1)]
+        if self.rank > 0:
+            ops_template += [(dist.isend, b["send_lo"], self.rank - 1), (dist.irecv, b["recv_lo"], self.rank - 1)]
         with torch.cuda.stream(self.stream):
             for _ in range(steps):
                 s.decomp_step_compute()
-                dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
+                dist.all_gather_into_tensor(b["headers_all"], b["header"], group=self.group)
+                s.decomp_step_pack()
+                ops = [dist.P2POp(op, t, self._peer(peer), group=self.group) for op, t, peer in ops_template]
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
                 s.decomp_step_commit()
+
+    def _peer(self, rank):
+        import torch.distributed as dist
+        if self.group is None:
+            return rank
+        return dist.get_global_rank(self.group, rank)
+
+    def gather_positions(self):
+        """All N positions on every rank (float64 [N, 3]): each rank contributes the beads it
+        owns.  Host-side (N x 24 bytes through the process group) -- for checks and output,
+        not part of a step."""
+        import torch
+        import torch.distributed as dist
+        own = self.sys.decomp_owned()
+        x = self.sys.get_positions(0)
+        x[~own] = 0.0
+        t = torch.from_numpy(np.concatenate([x, own[:, None].astype(np.float64)], axis=1)).cuda(self.device)
+        dist.all_reduce(t, group=self.group)
+        out = t.cpu().numpy()
+        if not np.all(out[:, 3] == 1.0):
+            raise RuntimeError("decomposition: %d beads are not owned exactly once"
+                               % int(np.sum(out[:, 3] != 1.0)))
+        return out[:, :3].copy()
+
+
+def _i32():
+    import torch
+    return torch.int32
 
 
 class LocalExchange:
-    """`world` contexts on ONE device standing in for `world` ranks: the all-gather is
-    a set of device-to-device copies.  Used by the single-GPU parity test."""
+    """`world` contexts on ONE device standing in for `world` ranks: the collectives are
+    device-to-device copies.  Used by the single-GPU parity tests."""
 
-    def __init__(self, systems, device=0):
+    def __init__(self, systems, device=0, halo_layers=None, halo_capacity=0):
         import torch
         self.systems = systems
         self.world = len(systems)
         for r, s in enumerate(systems):
             s.decomp_configure(r, self.world)
+            if halo_layers is not None or halo_capacity:
+                s.decomp_set_halo(halo_layers or 2, halo_capacity)
         self.bufs = [s.decomp_buffers(device) for s in systems]
-        self.elems = self.bufs[0][0].numel()
         self.torch = torch
 
     def begin(self, timestep, temperature=1.0):
@@ -60,14 +142,43 @@ class LocalExchange:
             s.run(0, timestep, temperature=temperature, restart=True)
 
     def step(self, steps=1):
+        H = HEADER_DOUBLES
         for _ in range(steps):
             for s in self.systems:
                 s.decomp_step_compute()
             for s in self.systems:
                 s.synchronize()
-            for _, recv in self.bufs:
-                for k, (send, _) in enumerate(self.bufs):
-                    recv[k * self.elems:(k + 1) * self.elems].copy_(send)
+            for b in self.bufs:
+                for k, src in enumerate(self.bufs):
+                    b["headers_all"][k * H:(k + 1) * H].copy_(src["header"])
+            self.torch.cuda.synchronize()
+            for s in self.systems:
+                s.decomp_step_pack()
+            for s in self.systems:
+                s.synchronize()
+            for k in range(self.world - 1):
+                self.bufs[k + 1]["recv_lo"].copy_(self.bufs[k]["send_hi"])
+                self.bufs[k]["recv_hi"].copy_(self.bufs[k + 1]["send_lo"])
             self.torch.cuda.synchronize()
             for s in self.systems:
                 s.decomp_step_commit()
+
+    def halo_counts(self):
+        out = []
+        for b in self.bufs:
+            out.append((int(b["send_lo"][:1].view(dtype=self.torch.int32).item()),
+                        int(b["send_hi"][:1].view(dtype=self.torch.int32).item())))
+        return out
+
+    def gather_positions(self):
+        """float64 [N, 3] merged from the beads each emulated rank owns."""
+        n = self.systems[0].n
+        x = np.zeros((n, 3))
+        owners = np.zeros(n, dtype=np.int32)
+        for s in self.systems:
+            own = s.decomp_owned()
+            x[own] = s.get_positions(0)[own]
+            owners += own
+        if not np.all(owners == 1):
+            raise RuntimeError("decomposition: %d beads are not owned exactly once" % int(np.sum(owners != 1)))
+        return x

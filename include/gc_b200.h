@@ -294,19 +294,42 @@ int gc_contacts_merge_device(gc_ctx *ctx, const uint64_t *keys_in, const uint32_
 
 /* ---- spatial decomposition of one large replica over several GPUs --------
    (BASELINE configs[4]; not in the reference, which is one process per cell.)
-   Every rank creates a context with n_replicas = 1 over ALL beads and calls
-   gc_decomp_configure(rank, world).  A step is then
-       gc_decomp_step_compute  -> all-gather of the send buffer into the receive
-       buffer (NCCL, on gc_stream)  -> gc_decomp_step_commit,
-   after gc_run(steps = 0, restart = 1) has set temperature / timestep.  The rank
-   evaluates and moves the sorted cell-list slots [rank C, (rank + 1) C), C =
-   ceil(n_beads / world); the trajectory is bit-identical for every world size.
-   Fixed timestep, no skin, no contact map.  world = 1 switches decomposition off. */
+   SLAB + HALO: every rank creates a context with n_replicas = 1 over ALL beads, calls
+   gc_decomp_configure(rank, world), gc_set_positions with all N beads and
+   gc_run(steps = 0, restart = 1).  Rank k then owns the z layers [z_k, z_k+1) of the cell grid
+   (equal-volume slabs of the bounding ellipsoid, re-derived every step from the global
+   bounding box) and keeps current copies of the beads within `layers` cell layers of its
+   slab.  One step is
+       gc_decomp_step_compute   cell list of the slab window, pair forces and the move of the
+                                owned beads, this rank's 128-byte header
+       all-gather               header -> headers_all over all ranks        (NCCL, gc_stream)
+       gc_decomp_step_pack      global reductions + the per-step callback body (next grid);
+                                moved beads near a slab face -> send_lo / send_hi
+       send/recv                send_hi -> rank + 1's recv_lo, send_lo -> rank - 1's recv_hi
+       gc_decomp_step_commit    received halo beads -> positions
+   Traffic per step and rank: two halo buffers out, two in (surface, not volume).  The
+   trajectory is bit-identical to the single-GPU one for every world size.  Fixed timestep,
+   no skin, no contact map.  Positions on one rank are only partly current afterwards: merge
+   the ranks with gc_decomp_owned + gc_get_positions.  gc_run(steps = 0, restart = 0)
+   refreshes parameters mid-run without touching the grid.  world = 1 switches it off.
+   Errors (reported by the next synchronising call): GC_ERR_STATE when a bonded partner, or a
+   bead after one step, lies outside the halo or a slab is thinner than the halo;
+   GC_ERR_CAPACITY when a halo buffer overflows. */
 int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world);
-/* Device buffers of float4: send = [elems], recv = [world][elems], elems = C + 2. */
-int gc_decomp_buffers(gc_ctx *ctx, void **send, void **recv, size_t *elems);
+/* Position halo in cell layers (default 2; bonded partners must lie within it) and beads per
+   halo buffer (0 keeps the current one; default min(N, 2 ceil(N / world))). */
+int gc_decomp_set_halo(gc_ctx *ctx, int32_t layers, int32_t capacity);
+/* Device buffers: four halo buffers of halo_elems float4 -- element 0 carries the bead count
+   in its first 4 bytes, then (x, y, z, bead) -- and the headers: header = 16 doubles,
+   headers_all = [world][16]. */
+int gc_decomp_buffers(gc_ctx *ctx, void **send_lo, void **send_hi, void **recv_lo, void **recv_hi,
+                      void **header, void **headers_all, size_t *halo_elems);
 int gc_decomp_step_compute(gc_ctx *ctx);
+int gc_decomp_step_pack(gc_ctx *ctx);
 int gc_decomp_step_commit(gc_ctx *ctx);
+/* mask[n_beads] (host): 1 for the beads this rank owns now; over all ranks every bead is
+   owned exactly once. */
+int gc_decomp_owned(gc_ctx *ctx, uint8_t *mask);
 
 /* ---- inter-stage transitions on the device ---------------------------------
    The reference runs `transition {interphase|prometaphase|cycle}` as a separate program

@@ -1,6 +1,6 @@
 """BASELINE.json configs[4]: one synthetic polymer spread over the GPUs of a box by the
-slot-range decomposition of csrc/gc_decomp.cuh, one NCCL all-gather of the new positions
-per step (SURVEY.md 8d "Config 5": 1 chain x N beads at config-4 density, fixed dt,
+slab + halo decomposition of csrc/gc_decomp.cuh: per step one all-gather of 128-byte headers
+and one NCCL send/recv of halo beads with each neighbouring rank (SURVEY.md 8d "Config 5": 1 chain x N beads at config-4 density, fixed dt,
 interphase force set).
   torchrun --nproc-per-node G --master-addr 127.0.0.1 scripts/run_decomp.py --beads 2000000
 Prints one JSON line on rank 0: decomposed ms/step (CUDA events, max over ranks), the same
@@ -26,6 +26,8 @@ ap.add_argument("--steps", type=int, default=100)
 ap.add_argument("--warmup", type=int, default=20)
 ap.add_argument("--check", action="store_true")
 ap.add_argument("--profile", type=int, default=0, help="per-kernel event timing over this many steps")
+ap.add_argument("--halo", type=int, default=3, help="position halo in cell layers")
+ap.add_argument("--cap-frac", type=float, default=0.0, help="halo buffer beads / (N / world); 0 = default")
 ap.add_argument("--out", default="")
 a = ap.parse_args()
 
@@ -73,14 +75,21 @@ rep = {"workload": f"1 chain x {design.n} beads, semiaxes {tuple(round(s, 2) for
 x_dec = None
 if world > 1:
     g = make()
-    run = decomp.DecomposedRun(g, rank, world, local)
+    run = decomp.DecomposedRun(g, rank, world, local, halo_layers=a.halo,
+                               halo_capacity=int(a.cap_frac * design.n / world))
     run.begin(cfg.timestep)
     run.step(a.warmup)
     ms = timed(lambda: run.step(a.steps), run.stream)
     g.synchronize()
     rep["decomposed_ms_per_step"] = ms / a.steps
     rep["decomposed_bead_steps_per_s"] = design.n * a.steps / (ms * 1e-3)
-    rep["exchange_bytes_per_rank_step"] = int(run.send.numel() * 4)
+    rep["scheme"] = run.scheme
+    rep["halo_layers"] = a.halo
+    rep["exchange_bytes_per_rank_step"] = int(run.exchange_bytes_per_step)
+    counts = torch.tensor(list(run.halo_counts()) + [int(g.decomp_owned().sum())], device=f"cuda:{local}")
+    allc = [torch.zeros_like(counts) for _ in range(world)]
+    dist.all_gather(allc, counts)
+    rep["halo_beads_sent_lo_hi_and_owned_per_rank"] = [c.tolist() for c in allc]
     if a.profile and rank == 0:
         g.profile_enable(True)
     if a.profile:
@@ -90,7 +99,7 @@ if world > 1:
         rep["decomposed_kernels_ms"] = {k: round(v[1] / a.profile, 5) for k, v in g.profile_read().items()}
         g.profile_enable(False)
     if a.check:
-        x_dec = g.get_positions(0)
+        x_dec = run.gather_positions()
     g.close()
 if rank == 0:
     g = make()
