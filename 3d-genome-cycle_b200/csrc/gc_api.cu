@@ -911,6 +911,8 @@ void launch_rebuild(gc_ctx *ctx)
         return;
     }
     dim3 g = bead_grid(ctx, 256);
+    // a decomposed run strides over the beads current on the rank
+    if (ctx->hp.decomp) g.x = std::min<unsigned>(g.x, 148 * 8);
     LAUNCH(ctx, k_count, g, 256, ctx->hp);
     LAUNCH(ctx, k_scan, dim3(ctx->hp.scan_blocks, ctx->n_rep), SCAN_BS, ctx->hp);
     LAUNCH(ctx, k_fill, g, 256, ctx->hp);
@@ -2005,6 +2007,22 @@ int decomp_alloc_halo(gc_ctx *ctx, int cap)
         if (rc) return rc;
         GC_CUDA(ctx, cudaMemsetAsync(b[k], 0, ((size_t) cap + 1) * sizeof(float4), ctx->stream));
     }
+    // the received halos are part of the next step's work list (decomp_current_bead): carry
+    // them over when the buffers are resized mid-run
+    const float4 *old_recv[2] = {P.drecv_lo, P.drecv_hi};
+    for (int k = 0; k < 2; k++) {
+        if (!old_recv[k]) continue;
+        int count = 0;
+        GC_CUDA(ctx, cudaMemcpyAsync(&count, old_recv[k], sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (count > cap) {
+            for (int j = 0; j < 4; j++) dev_free(ctx, b[j]);
+            return fail(ctx, GC_ERR_CAPACITY, "halo capacity %d is below the %d beads just received", cap, count);
+        }
+        GC_CUDA(ctx, cudaMemcpyAsync(b[2 + k], old_recv[k], ((size_t) count + 1) * sizeof(float4),
+                                     cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (P.dsend_lo) dev_free(ctx, P.dsend_lo);
     if (P.dsend_hi) dev_free(ctx, P.dsend_hi);
     if (P.drecv_lo) dev_free(ctx, const_cast<float4 *>(P.drecv_lo));
@@ -2102,9 +2120,8 @@ int gc_decomp_step_pack(gc_ctx *ctx)
 {
     GC_CHECK_CTX(ctx);
     if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
-    LAUNCH(ctx, k_decomp_reduce, 1, 32, ctx->hp);
     LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
-    LAUNCH(ctx, k_decomp_pack, (ctx->n + 255) / 256, 256, ctx->hp);
+    LAUNCH(ctx, k_decomp_pack, std::min((ctx->n + 255) / 256, 148 * 8), 256, ctx->hp);
     ctx->run_step++;
     ctx->parity ^= 1;
     return GC_OK;

@@ -16,7 +16,7 @@
 //                            share of the per-step reductions (bounding box, wall sums,
 //                            error) to a 128-byte header
 //   all-gather of the headers (world x 128 bytes; NCCL)
-//   gc_decomp_step_pack      k_decomp_reduce folds the headers in rank order, the per-step
+//   gc_decomp_step_pack      k_finalize_step folds the headers (decomp_reduce), its per-step
 //                            callback body plans the NEXT grid (identical on every rank);
 //                            k_decomp_pack appends each moved bead whose new layer lies
 //                            within dhalo layers of the neighbour's new slab -- or inside
@@ -37,8 +37,6 @@
 
 namespace gc {
 
-constexpr int DHDR = 16;     // doubles per rank header
-
 // after k_finish: this rank's share of the per-step reductions
 __global__ void k_decomp_header(const __grid_constant__ Params P)
 {
@@ -58,35 +56,13 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
     const int *start = P.cell_start;
     const int dxy = st.dims[0] * st.dims[1];
     hi[7] = start[st.zown_hi * dxy] - start[st.zown_lo * dxy];
+    // the work list of the next cell-list build: what this rank just moved (+ the halos)
+    st.dprev_lo = start[st.zown_lo * dxy];
+    st.dprev_hi = start[st.zown_hi * dxy];
+    st.dfull = 0;
     // the send buffers restart empty
     reinterpret_cast<int *>(P.dsend_lo)[0] = 0;
     reinterpret_cast<int *>(P.dsend_hi)[0] = 0;
-}
-
-// after the header all-gather: the reductions of the whole system, folded in rank order
-// (integer sums and min/max: order-independent anyway), then the per-step callback body
-__global__ void k_decomp_reduce(const __grid_constant__ Params P)
-{
-    GC_PDL_ENTRY();
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    RepState &st = P.st[0];
-    long long sum[4] = {0, 0, 0, 0};
-    int bmin[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
-    int bmax[3] = {(int) 0x80000000, (int) 0x80000000, (int) 0x80000000};
-    int err = 0, moved = 0;
-    for (int k = 0; k < P.dworld; k++) {
-        const double *h = P.dhdr_all + (size_t) k * DHDR;
-        const long long *hl = reinterpret_cast<const long long *>(h);
-        const int *hi = reinterpret_cast<const int *>(h + 4);
-        for (int c = 0; c < 4; c++) sum[c] += hl[c];
-        for (int c = 0; c < 3; c++) { bmin[c] = min(bmin[c], hi[c]); bmax[c] = max(bmax[c], hi[3 + c]); }
-        if (!err) err = hi[6];
-        moved += hi[7];
-    }
-    for (int c = 0; c < 3; c++) { st.axial_fx[c] = sum[c]; st.bbox_min[c] = bmin[c]; st.bbox_max[c] = bmax[c]; }
-    st.reaction_fx = sum[3];
-    if (!err && moved != P.n) err = 4;           // a bead was lost or moved twice
-    if (err) st.error = err;
 }
 
 // after the callback body planned the next grid: ship the moved beads the neighbours need
@@ -94,28 +70,37 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
 {
     GC_PDL_ENTRY();
     RepState &st = P.st[0];
-    const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= P.n) return;
-    // moved by this rank in the step just taken (halo copies keep the previous stamp)
-    if (P.dstamp[idx] != (int) st.step) return;
-    const float4 x = P.pos[st.parity][idx];
-    const int h = P.cells_per_cut;
-    const int layer = cell_layer(st, x.z, h);
-    const int z0 = slab_start(P.drank, P.dworld, st.gdimz, h);
-    const int z1 = slab_start(P.drank + 1, P.dworld, st.gdimz, h);
-    // a bead that jumped past a neighbour's whole slab would be lost
-    if (layer < slab_start(P.drank - 1, P.dworld, st.gdimz, h) ||
-        layer >= slab_start(P.drank + 2, P.dworld, st.gdimz, h)) {
-        atomicExch(&st.error, 3);
-    }
-    const float4 v = make_float4(x.x, x.y, x.z, __int_as_float(idx));
-    if (P.drank > 0 && layer < z0 + P.dhalo) {
-        const int k = atomicAdd(reinterpret_cast<int *>(P.dsend_lo), 1);
-        if (k < P.dcap) P.dsend_lo[1 + k] = v; else atomicExch(&st.error, 4);
-    }
-    if (P.drank + 1 < P.dworld && layer >= z1 - P.dhalo) {
-        const int k = atomicAdd(reinterpret_cast<int *>(P.dsend_hi), 1);
-        if (k < P.dcap) P.dsend_hi[1 + k] = v; else atomicExch(&st.error, 4);
+    __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2 in the NEW grid
+    if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P.drank - 1 + threadIdx.x, P.dworld, st.gdimz, P.cells_per_cut);
+    __syncthreads();
+    const int z0 = zs[1], z1 = zs[2];
+    const int lane = threadIdx.x & 31;
+    // the beads this rank moved in the step just taken: k_finish left them in the slot order
+    // of that step, in the sorted buffer of the parity that is current now
+    const int nw = st.dprev_hi - st.dprev_lo;
+    const int nw_pad = (nw + 31) & ~31;             // whole warps: the appends below are warp-aggregated
+    for (int w = blockIdx.x * 256 + threadIdx.x; w < nw_pad; w += gridDim.x * 256) {
+        const bool live = w < nw;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live) x = P.spos[st.parity][st.dprev_lo + w];   // new position, bead index in .w
+        const int layer = cell_layer(st, x.z, P.cells_per_cut);
+        // a bead that jumped past a neighbour's whole slab would be lost
+        if (live && (layer < zs[0] || layer >= zs[3])) atomicExch(&st.error, 3);
+        const bool to_lo = live && P.drank > 0 && layer < z0 + P.dhalo;
+        const bool to_hi = live && P.drank + 1 < P.dworld && layer >= z1 - P.dhalo;
+#pragma unroll
+        for (int side = 0; side < 2; side++) {
+            const unsigned m = __ballot_sync(0xffffffffu, side ? to_hi : to_lo);
+            if (!m) continue;
+            float4 *buf = side ? P.dsend_hi : P.dsend_lo;
+            int base = 0;
+            if (lane == __ffs(m) - 1) base = atomicAdd(reinterpret_cast<int *>(buf), __popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            if (side ? to_hi : to_lo) {
+                const int k = base + __popc(m & ((1u << lane) - 1u));
+                if (k < P.dcap) buf[1 + k] = x; else atomicExch(&st.error, 4);
+            }
+        }
     }
 }
 
@@ -143,6 +128,7 @@ __global__ void __launch_bounds__(256) k_decomp_stamp_all(const __grid_constant_
 {
     GC_PDL_ENTRY();
     const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i == 0) P.st[0].dfull = 1;
     if (i < P.n) P.dstamp[i] = (int) P.st[0].step;
 }
 

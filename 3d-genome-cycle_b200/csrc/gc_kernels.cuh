@@ -229,6 +229,35 @@ __global__ void k_bbox(const __grid_constant__ Params P)
 // beads inside a cell end up ordered by original index)
 // ---------------------------------------------------------------------------
 
+// Decomposed runs: the beads current on this rank, enumerated without touching the other
+// N - N / ranks beads (RepState::dfull / dprev_*).
+__device__ __forceinline__ int decomp_current_count(const Params &P, const RepState &st)
+{
+    if (st.dfull) return P.n;
+    int w = st.dprev_hi - st.dprev_lo;
+    if (P.drank > 0) w += min(reinterpret_cast<const int *>(P.drecv_lo)[0], P.dcap);
+    if (P.drank + 1 < P.dworld) w += min(reinterpret_cast<const int *>(P.drecv_hi)[0], P.dcap);
+    return w;
+}
+
+// (x, y, z, bead index bits) of work item w
+__device__ __forceinline__ float4 decomp_current_bead(const Params &P, const RepState &st, int w)
+{
+    if (st.dfull) {
+        float4 p = P.pos[st.parity][w];
+        p.w = __int_as_float(w);
+        return p;
+    }
+    const int na = st.dprev_hi - st.dprev_lo;
+    // k_finish left the moved beads in the slot order of the step just taken, in the sorted
+    // buffer of the parity that is current now (this step's k_gather overwrites it later)
+    if (w < na) return P.spos[st.parity][st.dprev_lo + w];
+    w -= na;
+    const int nlo = P.drank > 0 ? min(reinterpret_cast<const int *>(P.drecv_lo)[0], P.dcap) : 0;
+    if (w < nlo) return P.drecv_lo[1 + w];
+    return P.drecv_hi[1 + w - nlo];
+}
+
 __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
 {
     GC_PDL_ENTRY();
@@ -239,15 +268,26 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
     // reset the scan's look-back words, its ticket and the used-cell list
     if (i < P.scan_blocks) P.scan_status[(size_t) r * P.scan_blocks + i] = 0ull;
     if (i == 0) { P.st[r].scan_ticket = 0; P.st[r].n_used_cells = 0; P.st[r].n_light_cells = 0; }
-    if (i >= P.n) return;
-    int c = -1;
-    // a decomposed run bins the beads whose position is current on this rank
-    if (!P.decomp || P.dstamp[i] == (int) st.step) {
-        float4 p = P.pos[st.parity][(size_t) r * P.n + i];
-        c = cell_index(st, p, P.cells_per_cut);
+    if (P.decomp) {
+        // a decomposed run bins the beads whose position is current on this rank (grid-stride
+        // over that list; the grid need not cover N)
+        const int stride = gridDim.x * blockDim.x;
+        for (int k = i + stride; k < P.scan_blocks; k += stride) P.scan_status[k] = 0ull;
+        const int nw = decomp_current_count(P, st);
+        for (int w = i; w < nw; w += stride) {
+            const float4 p = decomp_current_bead(P, st, w);
+            const int b = __float_as_int(p.w);
+            const int c = cell_index(st, p, P.cells_per_cut);
+            P.cell_of[b] = c;
+            if (c >= 0) atomicAdd(&P.cell_count[c], 1);
+        }
+        return;
     }
+    if (i >= P.n) return;
+    float4 p = P.pos[st.parity][(size_t) r * P.n + i];
+    int c = cell_index(st, p, P.cells_per_cut);
     P.cell_of[(size_t) r * P.n + i] = c;
-    if (c >= 0) atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
+    atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
 }
 
 // Exclusive scan of the cell counts: chained multi-block scan with decoupled
@@ -360,9 +400,18 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
     const RepState &st = P.st[r];
     if (!st.need_rebuild) return;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (P.decomp) {
+        const int nw = decomp_current_count(P, st);
+        for (int w = i; w < nw; w += gridDim.x * blockDim.x) {
+            const int b = __float_as_int(decomp_current_bead(P, st, w).w);
+            const int c = P.cell_of[b];
+            if (c < 0) continue;
+            P.members[P.cell_start[c] + atomicAdd(&P.cell_count[c], 1)] = b;
+        }
+        return;
+    }
     if (i >= P.n) return;
     int c = P.cell_of[(size_t) r * P.n + i];
-    if (c < 0) return;
     int s = P.cell_start[(size_t) r * (P.ncell_max + 1) + c] +
             atomicAdd(&P.cell_count[(size_t) r * P.ncell_max + c], 1);
     P.members[(size_t) r * P.n + s] = i;
@@ -440,6 +489,12 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ Params P
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (P.decomp) {
+        // the grid need not cover N: stride over the slots this rank binned
+        const int total = P.cell_start[st.ncell];
+        for (; s < total; s += gridDim.x * blockDim.x) gather_slot(P, st, r, s);
+        return;
+    }
     if (s >= P.n) return;
     gather_slot(P, st, r, s);
 }

@@ -466,7 +466,12 @@ __device__ __forceinline__ void integrate_bead(const Params &P, const RepState &
     x.z = self4.z + fmaf(mudt, F.z, 0.5f * (W.z + Wp.z));
     x.w = 0.0f;
     P.pos[par ^ 1][ro + idx] = x;
-    if (P.decomp) P.dstamp[idx] = (int) n;          // current on this rank for step n (k_decomp_pack ships it)
+    if (P.decomp) {
+        P.dstamp[idx] = (int) n;                    // current on this rank for step n
+        // ... and in slot order with the bead index, for k_decomp_pack and the next cell-list
+        // build (decomp_current): neither then gathers from pos[]
+        P.spos[par ^ 1][t] = make_float4(x.x, x.y, x.z, self4.w);
+    }
     if (P.skin > 0.0f) {
         // cells may be reused: keep the sorted copy current and track the largest
         // displacement since the rebuild (neighbor_list.hpp:129-158)
@@ -557,6 +562,31 @@ __device__ __forceinline__ void repstate_store(RepState &dst, const RepState &sr
 }
 static_assert(sizeof(RepState) % sizeof(int) == 0, "RepState is copied word by word");
 
+constexpr int DHDR = 16;     // doubles per rank header of a decomposed run (gc_decomp.cuh)
+
+// Decomposed run, after the header all-gather: the reductions of the whole system, folded in
+// rank order (integer sums and min/max: order-independent anyway)
+__device__ inline void decomp_reduce(const Params &P, RepState &st)
+{
+    long long sum[4] = {0, 0, 0, 0};
+    int bmin[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+    int bmax[3] = {(int) 0x80000000, (int) 0x80000000, (int) 0x80000000};
+    int err = 0, moved = 0;
+    for (int k = 0; k < P.dworld; k++) {
+        const double *h = P.dhdr_all + (size_t) k * DHDR;
+        const long long *hl = reinterpret_cast<const long long *>(h);
+        const int *hi = reinterpret_cast<const int *>(h + 4);
+        for (int c = 0; c < 4; c++) sum[c] += hl[c];
+        for (int c = 0; c < 3; c++) { bmin[c] = min(bmin[c], hi[c]); bmax[c] = max(bmax[c], hi[3 + c]); }
+        if (!err) err = hi[6];
+        moved += hi[7];
+    }
+    for (int c = 0; c < 3; c++) { st.axial_fx[c] = sum[c]; st.bbox_min[c] = bmin[c]; st.bbox_max[c] = bmax[c]; }
+    st.reaction_fx = sum[3];
+    if (!err && moved != P.n) err = 4;           // a bead was lost or moved twice
+    if (err) st.error = err;
+}
+
 // after k_finish<STEP_FUSED> (fixed dt) or k_integrate (adaptive dt)
 __global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Params P, int adaptive)
 {
@@ -565,6 +595,7 @@ __global__ void __launch_bounds__(32) k_finalize_step(const __grid_constant__ Pa
     const int r = blockIdx.x, lane = threadIdx.x;
     repstate_load(s, P.st[r], lane);
     if (lane == 0) {
+        if (P.decomp) decomp_reduce(P, s);
         if (adaptive) {
             finalize_step(P, s, (double) s.sc.dt_cur);
         } else {

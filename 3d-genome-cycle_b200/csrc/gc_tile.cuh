@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P,
         const int dxy = st.dims[0] * st.dims[1];
         t_lo = start[st.zown_lo * dxy];
         t_hi = start[st.zown_hi * dxy];
+        if ((int) (blockIdx.x + 1) * BS <= t_lo || (int) blockIdx.x * BS >= t_hi) return;   // block-uniform
     }
     StepRed red;
     red_init(red);

@@ -172,6 +172,10 @@ struct RepState {
     // z-window of a decomposed run: dims[2] counts the LOCAL layers [zoff, zoff + dims[2]) of the
     // global grid (gdimz layers); the local layers [zown_lo, zown_hi) are owned by this rank
     int zoff, gdimz, zown_lo, zown_hi;
+    // the beads current on this rank, as a work list for the next cell-list build: the sorted
+    // slots [dprev_lo, dprev_hi) it moved in the last step (bead index in spos[].w) plus the
+    // two received halo buffers; dfull = 1: all N beads (after gc_run(restart = 1))
+    int dfull, dprev_lo, dprev_hi;
     StepConst sc;
 };
 

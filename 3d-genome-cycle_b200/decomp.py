@@ -45,16 +45,35 @@ class DecomposedRun:
         self.device = device
         system.decomp_configure(rank, world)
         self.buf = None
+        self.halo_layers = halo_layers or 2
         if world > 1:
             if halo_layers is not None or halo_capacity:
-                system.decomp_set_halo(halo_layers or 2, halo_capacity)
+                system.decomp_set_halo(self.halo_layers, halo_capacity)
             self.buf = system.decomp_buffers(device)
         self.stream = torch.cuda.ExternalStream(system.stream(), device=device)
 
     def begin(self, timestep, temperature=1.0):
         """Temperature / timestep, restart, first grid plan (gc_run with 0 steps); every rank
         must have been given all N positions."""
+        self._run_args = (timestep, temperature)
         self.sys.run(0, timestep, temperature=temperature, restart=True)
+
+    def tune_capacity(self, slack=1.5, floor=1024):
+        """Shrinks the halo buffers (whole buffers travel every step) to `slack` x the largest
+        halo any rank shipped in the last step; call after a few warm-up steps.  Collective."""
+        import torch
+        import torch.distributed as dist
+        if self.world == 1:
+            return 0
+        self.sys.synchronize()
+        t = torch.tensor([max(self.halo_counts())], device=f"cuda:{self.device}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        cap = int(slack * int(t.item())) + floor
+        self.sys.decomp_set_halo(self.halo_layers, cap)
+        timestep, temperature = self._run_args
+        self.sys.run(0, timestep, temperature=temperature, restart=False)   # parameters only
+        self.buf = self.sys.decomp_buffers(self.device)
+        return cap
 
     @property
     def exchange_bytes_per_step(self):
@@ -134,6 +153,7 @@ class LocalExchange:
             s.decomp_configure(r, self.world)
             if halo_layers is not None or halo_capacity:
                 s.decomp_set_halo(halo_layers or 2, halo_capacity)
+        self.device = device
         self.bufs = [s.decomp_buffers(device) for s in systems]
         self.torch = torch
 
@@ -162,6 +182,14 @@ class LocalExchange:
             self.torch.cuda.synchronize()
             for s in self.systems:
                 s.decomp_step_commit()
+
+    def set_halo(self, layers, capacity, timestep, temperature=1.0):
+        """Resizes every rank's halo buffers between two steps."""
+        for s in self.systems:
+            s.synchronize()
+            s.decomp_set_halo(layers, capacity)
+            s.run(0, timestep, temperature=temperature, restart=False)   # parameters only
+        self.bufs = [s.decomp_buffers(self.device) for s in self.systems]
 
     def halo_counts(self):
         out = []

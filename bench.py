@@ -815,9 +815,14 @@ def decomp_block(gc_b200, args, rank, world, local):
         return s
 
     g = make()
-    run = decomp.DecomposedRun(g, rank, world, local)
+    # the walk's bonds (0.3) span two cell edges (0.15): a three-layer position halo; halo
+    # buffers sized for the beads of ~half a slab (the library reports an overflow)
+    run = decomp.DecomposedRun(g, rank, world, local, halo_layers=3,
+                               halo_capacity=max(1024, int(0.6 * beads / world)))
     run.begin(cfg.timestep)
-    run.step(warm)
+    run.step(warm // 2)
+    cap = run.tune_capacity()
+    run.step(warm - warm // 2)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     dist.barrier()
     torch.cuda.synchronize()
@@ -829,9 +834,12 @@ def decomp_block(gc_b200, args, rank, world, local):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     g.synchronize()
-    x_dec = run.gather_positions() if hasattr(run, "gather_positions") else g.get_positions(0)
-    exch = run.exchange_bytes_per_step() if hasattr(run, "exchange_bytes_per_step") else int(run.send.numel() * 4)
-    scheme = getattr(run, "scheme", "replicated positions + all-gather")
+    x_dec = run.gather_positions()
+    counts = torch.tensor(list(run.halo_counts()) + [int(g.decomp_owned().sum())], device=f"cuda:{local}")
+    allc = [torch.zeros_like(counts) for _ in range(world)]
+    dist.all_gather(allc, counts)
+    exch = int(run.exchange_bytes_per_step)
+    scheme = run.scheme
     g.close()
     out = None
     if rank == 0:
@@ -851,7 +859,9 @@ def decomp_block(gc_b200, args, rank, world, local):
                "scheme": scheme, "steps": steps, "warmup": warm,
                "ms_per_step": ms / steps, "bead_steps_per_s": design.n * steps / (ms * 1e-3),
                "single_gpu_ms_per_step": ms1 / steps, "speedup_vs_single_gpu": ms1 / ms,
-               "exchange_bytes_per_rank_step": exch, "bit_identical_to_single_gpu": same,
+               "exchange_bytes_per_rank_step": exch, "halo_layers": 3, "halo_capacity_beads": cap,
+               "halo_beads_lo_hi_and_owned_per_rank": [c.tolist() for c in allc],
+               "bit_identical_to_single_gpu": same,
                "timing": "CUDA events on the library's stream, max over ranks"}
     dist.barrier()
     return out

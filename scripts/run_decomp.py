@@ -78,7 +78,9 @@ if world > 1:
     run = decomp.DecomposedRun(g, rank, world, local, halo_layers=a.halo,
                                halo_capacity=int(a.cap_frac * design.n / world))
     run.begin(cfg.timestep)
-    run.step(a.warmup)
+    run.step(a.warmup // 2)
+    rep["halo_capacity_beads"] = run.tune_capacity()
+    run.step(a.warmup - a.warmup // 2)
     ms = timed(lambda: run.step(a.steps), run.stream)
     g.synchronize()
     rep["decomposed_ms_per_step"] = ms / a.steps

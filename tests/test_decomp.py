@@ -125,7 +125,11 @@ def test_decomposed_200k_polymer_is_bit_identical_and_exchanges_a_surface(world)
     # the walk's bonds (0.3) span two cell edges (0.15): a three-layer position halo
     ex = decomp.LocalExchange(ranks, halo_layers=3)
     ex.begin(cfg.timestep)
-    ex.step(steps)
+    ex.step(steps // 2)
+    # resizing the halo buffers mid-run keeps the halos just received
+    cap = int(1.5 * max(max(c) for c in ex.halo_counts())) + 1024
+    ex.set_halo(3, cap, cfg.timestep)
+    ex.step(steps - steps // 2)
     np.testing.assert_array_equal(ex.gather_positions(), xr)
     owned = [int(g.decomp_owned().sum()) for g in ranks]
     assert sum(owned) == n
