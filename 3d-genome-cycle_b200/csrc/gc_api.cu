@@ -2136,6 +2136,15 @@ int gc_decomp_step_commit(gc_ctx *ctx)
     return GC_OK;
 }
 
+int gc_decomp_host_advance(gc_ctx *ctx, int64_t steps)
+{
+    GC_CHECK_CTX(ctx);
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    ctx->run_step += steps;
+    if (steps & 1) ctx->parity ^= 1;
+    return GC_OK;
+}
+
 int gc_decomp_owned(gc_ctx *ctx, uint8_t *mask)
 {
     GC_CHECK_CTX(ctx);

@@ -39,12 +39,15 @@ class DecomposedRun:
     scheme = "z-slabs of the cell grid + halo exchange with the two neighbouring ranks"
 
     def __init__(self, system, rank: int, world: int, device: int = 0, group=None,
-                 halo_layers: int | None = None, halo_capacity: int = 0):
+                 halo_layers: int | None = None, halo_capacity: int = 0, graph_steps: int = 0):
         import torch
         self.sys, self.rank, self.world, self.group = system, rank, world, group
         self.device = device
         system.decomp_configure(rank, world)
         self.buf = None
+        self.graph_steps = int(graph_steps)
+        self._graph = None
+        self._eager_done = False
         self.halo_layers = halo_layers or 2
         if world > 1:
             if halo_layers is not None or halo_capacity:
@@ -73,6 +76,7 @@ class DecomposedRun:
         timestep, temperature = self._run_args
         self.sys.run(0, timestep, temperature=temperature, restart=False)   # parameters only
         self.buf = self.sys.decomp_buffers(self.device)
+        self._graph = None
         return cap
 
     @property
@@ -92,25 +96,57 @@ class DecomposedRun:
         return lo, hi
 
     def step(self, steps=1):
+        """Advances `steps` steps.  With graph_steps > 0 (constructor), whole blocks of that
+        many steps -- kernels and NCCL operations alike -- are replayed from one CUDA graph
+        captured on first use; the remainder runs eagerly."""
         import torch
-        import torch.distributed as dist
-        s, b = self.sys, self.buf
         if self.world == 1:
             raise RuntimeError("world = 1: use System.run")
+        K = self.graph_steps
+        with torch.cuda.stream(self.stream):
+            while K and steps >= K and self._eager_done:
+                if self._graph is None:
+                    self._capture(K)
+                self._graph.replay()
+                self.sys.decomp_host_advance(K)
+                steps -= K
+            self._eager(steps)
+
+    def _capture(self, K):
+        import torch
+        self.sys.synchronize()              # (eager steps came first: the communicators are live)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self.stream, capture_error_mode="thread_local"):
+            self._eager(K)
+        self.sys.decomp_host_advance(-K)    # the capture moved the host mirror, not the device
+        self._graph = g
+
+    def invalidate_graph(self):
+        """After anything that changes buffers or parameters (tune_capacity, set_context ...);
+        also before the process group is destroyed (a live graph holds NCCL kernels)."""
+        import torch
+        if self._graph is not None:
+            torch.cuda.synchronize()
+            self._graph = None
+
+    def _eager(self, steps):
+        import torch.distributed as dist
+        s, b = self.sys, self.buf
         ops_template = []
         if self.rank + 1 < self.world:
             ops_template += [(dist.isend, b["send_hi"], self.rank + 1), (dist.irecv, b["recv_hi"], self.rank + 1)]
         if self.rank > 0:
             ops_template += [(dist.isend, b["send_lo"], self.rank - 1), (dist.irecv, b["recv_lo"], self.rank - 1)]
-        with torch.cuda.stream(self.stream):
-            for _ in range(steps):
-                s.decomp_step_compute()
-                dist.all_gather_into_tensor(b["headers_all"], b["header"], group=self.group)
-                s.decomp_step_pack()
-                ops = [dist.P2POp(op, t, self._peer(peer), group=self.group) for op, t, peer in ops_template]
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
-                s.decomp_step_commit()
+        if steps > 0:
+            self._eager_done = True
+        for _ in range(steps):
+            s.decomp_step_compute()
+            dist.all_gather_into_tensor(b["headers_all"], b["header"], group=self.group)
+            s.decomp_step_pack()
+            ops = [dist.P2POp(op, t, self._peer(peer), group=self.group) for op, t, peer in ops_template]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            s.decomp_step_commit()
 
     def _peer(self, rank):
         import torch.distributed as dist

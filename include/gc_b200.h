@@ -327,6 +327,13 @@ int gc_decomp_buffers(gc_ctx *ctx, void **send_lo, void **send_hi, void **recv_l
 int gc_decomp_step_compute(gc_ctx *ctx);
 int gc_decomp_step_pack(gc_ctx *ctx);
 int gc_decomp_step_commit(gc_ctx *ctx);
+/* The three step calls only enqueue kernels, so a block of steps -- with the caller's
+   collectives between them -- can be captured into a CUDA graph on gc_stream and replayed.
+   The library keeps a host-side mirror of the step count and of the position buffer in use:
+   a capture advances it without running anything, a replay runs without advancing it.
+   gc_decomp_host_advance(ctx, k) corrects the mirror by k steps (k < 0 after a capture of
+   -k steps, k > 0 after every replay). */
+int gc_decomp_host_advance(gc_ctx *ctx, int64_t steps);
 /* mask[n_beads] (host): 1 for the beads this rank owns now; over all ranks every bead is
    owned exactly once. */
 int gc_decomp_owned(gc_ctx *ctx, uint8_t *mask);

@@ -28,6 +28,7 @@ ap.add_argument("--check", action="store_true")
 ap.add_argument("--profile", type=int, default=0, help="per-kernel event timing over this many steps")
 ap.add_argument("--halo", type=int, default=3, help="position halo in cell layers")
 ap.add_argument("--cap-frac", type=float, default=0.0, help="halo buffer beads / (N / world); 0 = default")
+ap.add_argument("--graph", type=int, default=0, help="steps per CUDA graph (0: eager)")
 ap.add_argument("--out", default="")
 a = ap.parse_args()
 
@@ -76,12 +77,23 @@ x_dec = None
 if world > 1:
     g = make()
     run = decomp.DecomposedRun(g, rank, world, local, halo_layers=a.halo,
-                               halo_capacity=int(a.cap_frac * design.n / world))
+                               halo_capacity=int(a.cap_frac * design.n / world),
+                               graph_steps=a.graph)
     run.begin(cfg.timestep)
     run.step(a.warmup // 2)
     rep["halo_capacity_beads"] = run.tune_capacity()
     run.step(a.warmup - a.warmup // 2)
-    ms = timed(lambda: run.step(a.steps), run.stream)
+    import time
+    enq = [0.0]
+
+    def block():
+        t0 = time.perf_counter()
+        run.step(a.steps)
+        enq[0] = time.perf_counter() - t0
+
+    ms = timed(block, run.stream)
+    rep["graph_steps"] = a.graph
+    rep["host_enqueue_ms_per_step"] = enq[0] * 1e3 / a.steps
     g.synchronize()
     rep["decomposed_ms_per_step"] = ms / a.steps
     rep["decomposed_bead_steps_per_s"] = design.n * a.steps / (ms * 1e-3)
@@ -100,6 +112,7 @@ if world > 1:
     if a.profile and rank == 0:
         rep["decomposed_kernels_ms"] = {k: round(v[1] / a.profile, 5) for k, v in g.profile_read().items()}
         g.profile_enable(False)
+    run.invalidate_graph()
     if a.check:
         x_dec = run.gather_positions()
     g.close()
