@@ -117,6 +117,7 @@ SYMBOLS = [
     ("gc_decomp_step_pack", C.c_int, [_P]),
     ("gc_decomp_owned", C.c_int, [_P, C.c_void_p]),
     ("gc_decomp_host_advance", C.c_int, [_P, C.c_int64]),
+    ("gc_decomp_set_owned_bound", C.c_int, [_P, C.c_int32]),
     ("gc_decomp_step_compute", C.c_int, [_P]),
     ("gc_decomp_step_commit", C.c_int, [_P]),
     ("gc_transition_interphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, C.c_int32, _ip, C.c_int32]),
@@ -510,6 +511,9 @@ class System:
 
     def decomp_step_pack(self):
         self._ck(self.lib.gc_decomp_step_pack(self._h))
+
+    def decomp_set_owned_bound(self, beads):
+        self._ck(self.lib.gc_decomp_set_owned_bound(self._h, int(beads)))
 
     def decomp_host_advance(self, steps):
         self._ck(self.lib.gc_decomp_host_advance(self._h, int(steps)))

@@ -942,7 +942,8 @@ int check_device_errors(gc_ctx *ctx)
         }
         if (st[r].error == 4) {
             return fail(ctx, GC_ERR_CAPACITY, "decomposed run, step %lld: halo buffer full (%d beads; "
-                        "gc_decomp_set_halo) or the ranks' bead counts do not add up", st[r].step,
+                        "gc_decomp_set_halo), a rank owns more than gc_decomp_set_owned_bound allows, "
+                        "or the ranks' bead counts do not add up", st[r].step,
                         ctx->hp.dcap);
         }
     }
@@ -2066,6 +2067,7 @@ int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world)
     P.drank = rank;
     P.dworld = world;
     P.dhalo = std::max(2, P.cells_per_cut);
+    P.down_bound = ctx->n;
     return GC_OK;
 }
 
@@ -2078,6 +2080,15 @@ int gc_decomp_set_halo(gc_ctx *ctx, int32_t layers, int32_t capacity)
     P.dhalo = layers;
     ctx->params_dirty = true;
     if (capacity > 0 && capacity != P.dcap) return decomp_alloc_halo(ctx, capacity);
+    return GC_OK;
+}
+
+int gc_decomp_set_owned_bound(gc_ctx *ctx, int32_t beads)
+{
+    GC_CHECK_CTX(ctx);
+    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    ctx->hp.down_bound = beads > 0 ? std::min(beads, ctx->n) : ctx->n;
+    ctx->params_dirty = true;
     return GC_OK;
 }
 
@@ -2111,7 +2122,7 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
     launch_rebuild(ctx);
     launch_pair(ctx, 0u, 1);
-    LAUNCH(ctx, k_finish<STEP_FUSED>, dim3((ctx->n + BS - 1) / BS, 1), BS, ctx->hp, 0u, 1);
+    LAUNCH(ctx, k_finish<STEP_FUSED>, dim3((P.down_bound + BS - 1) / BS, 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);
     return GC_OK;
 }

@@ -56,6 +56,7 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
     const int *start = P.cell_start;
     const int dxy = st.dims[0] * st.dims[1];
     hi[7] = start[st.zown_hi * dxy] - start[st.zown_lo * dxy];
+    if (hi[7] > P.down_bound && !hi[6]) hi[6] = st.error = 4;      // k_finish's grid did not reach them all
     // the work list of the next cell-list build: what this rank just moved (+ the halos)
     st.dprev_lo = start[st.zown_lo * dxy];
     st.dprev_hi = start[st.zown_hi * dxy];

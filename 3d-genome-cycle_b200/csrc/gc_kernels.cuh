@@ -306,6 +306,9 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan(const __grid_constant__ Params
     const int r = blockIdx.y;
     RepState &st = P.st[r];
     if (!st.need_rebuild) return;
+    // the grid is sized for ncell_max: only as many blocks as the grid has tiles take a ticket
+    // (the others would only queue up on the ticket word)
+    if ((int) blockIdx.x * SCAN_TILE >= st.ncell) return;
     __shared__ int warp_sums[SCAN_BS / 32];
     __shared__ int sh_bid, sh_excl;
     if (threadIdx.x == 0) sh_bid = atomicAdd(&st.scan_ticket, 1);

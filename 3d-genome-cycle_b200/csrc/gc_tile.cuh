@@ -21,15 +21,18 @@ __global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P,
     RepState &st = P.st[r];
     const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
     // a decomposed run moves the sorted slots of the layers it owns (contiguous: z is the
-    // slowest cell axis); the grid covers all N slots, the other threads have nothing to do
-    const int t = blockIdx.x * BS + threadIdx.x;
+    // slowest cell axis)
+    int t = blockIdx.x * BS + threadIdx.x;
     int t_lo = 0, t_hi = P.n;
     if (P.decomp) {
+        // the grid covers Params::down_bound slots from the first owned one (k_decomp_header
+        // reports a rank that owns more)
         const int *start = P.cell_start + (size_t) r * (P.ncell_max + 1);
         const int dxy = st.dims[0] * st.dims[1];
         t_lo = start[st.zown_lo * dxy];
         t_hi = start[st.zown_hi * dxy];
-        if ((int) (blockIdx.x + 1) * BS <= t_lo || (int) blockIdx.x * BS >= t_hi) return;   // block-uniform
+        t += t_lo;
+        if ((int) blockIdx.x * BS >= t_hi - t_lo) return;   // block-uniform
     }
     StepRed red;
     red_init(red);

@@ -227,6 +227,7 @@ struct Params {
     int drank, dworld;             // this rank, ranks
     int dhalo;                     // position halo in cell layers (>= 1; bonded partners must lie inside)
     int dcap;                      // beads per halo buffer
+    int down_bound;                // bound on the beads a rank owns (sizes k_finish's grid)
     int *dstamp;                   // [N] step at which pos[] of a bead was last written on this rank
     float4 *dsend_lo, *dsend_hi;   // [dcap + 1] (x, y, z, bead) for rank - 1 / rank + 1; [0].x = count bits
     const float4 *drecv_lo, *drecv_hi;   // the same, received from rank - 1 / rank + 1

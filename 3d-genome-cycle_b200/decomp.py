@@ -63,16 +63,19 @@ class DecomposedRun:
 
     def tune_capacity(self, slack=1.5, floor=1024):
         """Shrinks the halo buffers (whole buffers travel every step) to `slack` x the largest
-        halo any rank shipped in the last step; call after a few warm-up steps.  Collective."""
+        halo any rank shipped in the last step, and the per-bead kernel's grid to `slack` x the
+        largest bead count any rank owns; call after a few warm-up steps.  Collective."""
         import torch
         import torch.distributed as dist
         if self.world == 1:
             return 0
         self.sys.synchronize()
-        t = torch.tensor([max(self.halo_counts())], device=f"cuda:{self.device}")
+        t = torch.tensor([max(self.halo_counts()), int(self.sys.decomp_owned().sum())],
+                         device=f"cuda:{self.device}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-        cap = int(slack * int(t.item())) + floor
+        cap = int(slack * int(t[0].item())) + floor
         self.sys.decomp_set_halo(self.halo_layers, cap)
+        self.sys.decomp_set_owned_bound(int(slack * int(t[1].item())) + floor)
         timestep, temperature = self._run_args
         self.sys.run(0, timestep, temperature=temperature, restart=False)   # parameters only
         self.buf = self.sys.decomp_buffers(self.device)

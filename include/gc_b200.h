@@ -319,6 +319,9 @@ int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world);
 /* Position halo in cell layers (default 2; bonded partners must lie within it) and beads per
    halo buffer (0 keeps the current one; default min(N, 2 ceil(N / world))). */
 int gc_decomp_set_halo(gc_ctx *ctx, int32_t layers, int32_t capacity);
+/* Upper bound on the beads one rank owns (default, and 0: n_beads); the per-bead kernel's grid
+   is sized by it.  A rank that owns more reports GC_ERR_CAPACITY. */
+int gc_decomp_set_owned_bound(gc_ctx *ctx, int32_t beads);
 /* Device buffers: four halo buffers of halo_elems float4 -- element 0 carries the bead count
    in its first 4 bytes, then (x, y, z, bead) -- and the headers: header = 16 doubles,
    headers_all = [world][16]. */
