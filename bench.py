@@ -818,7 +818,7 @@ def decomp_block(gc_b200, args, rank, world, local):
     # the walk's bonds (0.3) span two cell edges (0.15): a three-layer position halo; halo
     # buffers sized for the beads of ~half a slab (the library reports an overflow)
     run = decomp.DecomposedRun(g, rank, world, local, halo_layers=3,
-                               halo_capacity=max(1024, int(0.6 * beads / world)))
+                               halo_capacity=max(1024, int(0.6 * beads / world)), graph_steps=10)
     run.begin(cfg.timestep)
     run.step(warm // 2)
     cap = run.tune_capacity()
@@ -834,6 +834,7 @@ def decomp_block(gc_b200, args, rank, world, local):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     g.synchronize()
+    run.invalidate_graph()          # a live graph holds NCCL kernels
     x_dec = run.gather_positions()
     counts = torch.tensor(list(run.halo_counts()) + [int(g.decomp_owned().sum())], device=f"cuda:{local}")
     allc = [torch.zeros_like(counts) for _ in range(world)]
@@ -862,6 +863,7 @@ def decomp_block(gc_b200, args, rank, world, local):
                "exchange_bytes_per_rank_step": exch, "halo_layers": 3, "halo_capacity_beads": cap,
                "halo_beads_lo_hi_and_owned_per_rank": [c.tolist() for c in allc],
                "bit_identical_to_single_gpu": same,
+               "graph_steps": 10,
                "timing": "CUDA events on the library's stream, max over ranks"}
     dist.barrier()
     return out
