@@ -151,6 +151,39 @@ class DecomposedRun:
                 w.wait()
             s.decomp_step_commit()
 
+    def timed_phases(self, steps=20):
+        """Eager steps with CUDA events between the phases: mean ms of (compute, header
+        all-gather, pack, halo send/recv, commit) on this rank.  The collectives' figures
+        include the wait for the slowest rank."""
+        import torch
+        import torch.distributed as dist
+        s, b = self.sys, self.buf
+        names = ("compute", "header_all_gather", "pack", "halo_send_recv", "commit")
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(steps)]
+        with torch.cuda.stream(self.stream):
+            for k in range(steps):
+                ev[k][0].record(self.stream)
+                s.decomp_step_compute()
+                ev[k][1].record(self.stream)
+                dist.all_gather_into_tensor(b["headers_all"], b["header"], group=self.group)
+                ev[k][2].record(self.stream)
+                s.decomp_step_pack()
+                ev[k][3].record(self.stream)
+                ops = []
+                if self.rank + 1 < self.world:
+                    ops += [dist.P2POp(dist.isend, b["send_hi"], self._peer(self.rank + 1), group=self.group),
+                            dist.P2POp(dist.irecv, b["recv_hi"], self._peer(self.rank + 1), group=self.group)]
+                if self.rank > 0:
+                    ops += [dist.P2POp(dist.isend, b["send_lo"], self._peer(self.rank - 1), group=self.group),
+                            dist.P2POp(dist.irecv, b["recv_lo"], self._peer(self.rank - 1), group=self.group)]
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+                ev[k][4].record(self.stream)
+                s.decomp_step_commit()
+                ev[k][5].record(self.stream)
+        s.synchronize()
+        return {n: sum(e[i].elapsed_time(e[i + 1]) for e in ev) / steps for i, n in enumerate(names)}
+
     def _peer(self, rank):
         import torch.distributed as dist
         if self.group is None:

@@ -104,6 +104,11 @@ if world > 1:
     allc = [torch.zeros_like(counts) for _ in range(world)]
     dist.all_gather(allc, counts)
     rep["halo_beads_sent_lo_hi_and_owned_per_rank"] = [c.tolist() for c in allc]
+    if a.profile:
+        ph = run.timed_phases(a.profile)
+        allp = [None] * world
+        dist.all_gather_object(allp, ph)
+        rep["phase_ms_per_rank"] = [{k: round(v, 5) for k, v in p.items()} for p in allp]
     if a.profile and rank == 0:
         g.profile_enable(True)
     if a.profile:
