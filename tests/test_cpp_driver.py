@@ -16,14 +16,27 @@ SRC = ROOT / "examples" / "interphase_driver.cpp"
 EXE = ROOT / "examples" / "interphase_driver"
 
 
-def build_driver():
+def build_driver(name="interphase_driver"):
     lib = gc_b200.build.build()
-    deps = [SRC, ROOT / "include" / "gc_md.hpp", ROOT / "include" / "gc_b200.h"]
-    if EXE.exists() and all(EXE.stat().st_mtime >= d.stat().st_mtime for d in deps):
-        return EXE
-    subprocess.run(["g++", "-std=c++20", "-O2", "-Wall", "-o", str(EXE), str(SRC),
+    src, exe = ROOT / "examples" / f"{name}.cpp", ROOT / "examples" / name
+    deps = [src, ROOT / "examples" / "mitotic_common.hpp", ROOT / "include" / "gc_md.hpp",
+            ROOT / "include" / "gc_b200.h"]
+    if exe.exists() and all(exe.stat().st_mtime >= d.stat().st_mtime for d in deps):
+        return exe
+    subprocess.run(["g++", "-std=c++20", "-O2", "-Wall", "-o", str(exe), str(src),
                     f"-L{lib.parent}", "-lgc_b200", "-Wl,-rpath," + str(lib.parent)], check=True)
-    return EXE
+    return exe
+
+
+def write_mitotic_design(path, md, x):
+    with open(path, "wb") as f:
+        f.write(b"GCM1")
+        f.write(struct.pack("<iii", md.n, len(md.chains), len(md.sisters)))
+        f.write(np.ascontiguousarray(md.chains, dtype="<i4").tobytes())
+        f.write(np.ascontiguousarray(md.kinetochores, dtype="<i4").tobytes())
+        f.write(np.ascontiguousarray(md.sisters, dtype="<i4").tobytes())
+        f.write(np.ascontiguousarray(md.poles, dtype="<f8").tobytes())
+        f.write(np.ascontiguousarray(x, dtype="<f8").tobytes())
 
 
 def write_design(path, d, x):
@@ -92,3 +105,82 @@ def test_cpp_driver_matches_python_driver(tmp_path):
     assert list(tail[1:4]) == list(c.semiaxes)
     assert tail[6] == pytest.approx(g.compute_energy() / d.n, rel=1e-12)
     assert len(contacts) > 0
+
+
+def _mitotic_inputs(sisters):
+    synth = gc_b200.synth
+    d, _, _ = small_interphase(scale=0.3, radius=1.0)
+    mcfg = synth.MitoticConfig()
+    md = synth.make_mitotic_design(d, mcfg, sisters=sisters)
+    x = synth.quantize_f32(synth.rod_positions(md, mcfg, seed=3)).astype(np.float64)
+    return md, mcfg, x
+
+
+def test_mitotic_drivers_build_and_fail_loudly_without_gpu(tmp_path):
+    import torch
+    exes = [build_driver("anatelophase_driver"), build_driver("prometaphase_driver")]
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    md, mcfg, x = _mitotic_inputs(sisters=False)
+    write_mitotic_design(tmp_path / "in.bin", md, x)
+    for exe, tail in zip(exes, (["1", "1", "1", "2"], ["1", "1"])):
+        p = subprocess.run([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "out.bin")] + tail,
+                           capture_output=True, text=True)
+        assert p.returncode == 1 and "error:" in p.stderr
+        assert not (tmp_path / "out.bin").exists()
+
+
+@pytest.mark.gpu
+def test_cpp_anatelophase_driver_matches_python_driver(tmp_path):
+    """Dragging stage, then the runtime swap dragging -> packing and anaphase -> telophase
+    bonded terms (disable()/enable() of registered force fields): bit-identical to the same
+    calls from stages.py."""
+    exe = build_driver("anatelophase_driver")
+    md, mcfg, x = _mitotic_inputs(sisters=False)
+    n_ana, n_telo, s_ana, s_telo = 150, 90, 11, 12
+    write_mitotic_design(tmp_path / "in.bin", md, x)
+    p = subprocess.run([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), str(n_ana),
+                        str(n_telo), str(s_ana), str(s_telo), "50"], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    assert p.stderr.count("[anaphase]") == 3 and p.stderr.count("[telophase]") == 2
+    pos, tail, _ = read_output(tmp_path / "out.bin")
+
+    g = gc_b200.System(md.n, 1, 0)
+    t = stages.setup_anatelophase(g, md, mcfg)
+    g.set_positions(x)
+    stages.enter_anaphase(g, t)
+    g.set_seeds([s_ana])
+    g.run(n_ana, mcfg.timestep)
+    stages.enter_telophase(g, t)
+    g.set_seeds([s_telo])
+    g.run(n_telo, mcfg.timestep)
+    np.testing.assert_array_equal(pos, g.get_positions())
+    assert tail[0] == g.get_context().time
+    assert tail[6] == pytest.approx(g.compute_energy() / md.n, rel=1e-12)
+    assert np.abs(pos - x).max() > 0.05          # the stage did move the chromosomes
+    g.close()
+
+
+@pytest.mark.gpu
+def test_cpp_prometaphase_driver_matches_python_driver(tmp_path):
+    """Sister bonds, one k-fibre force field per pole and polar ejection with f != 0."""
+    import dataclasses
+    exe = build_driver("prometaphase_driver")
+    md, mcfg, x = _mitotic_inputs(sisters=True)
+    mcfg = dataclasses.replace(mcfg, polar_ejection_force=0.8, polar_ejection_cross_section=0.25)
+    steps, seed = 160, 21
+    write_mitotic_design(tmp_path / "in.bin", md, x)
+    p = subprocess.run([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), str(steps),
+                        str(seed), "40", "0.8", "0.25"], capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    assert p.stderr.count("[prometaphase]") == 4
+    pos, tail, _ = read_output(tmp_path / "out.bin")
+
+    g = gc_b200.System(md.n, 1, 0)
+    stages.setup_prometaphase(g, md, mcfg)
+    g.set_positions(x)
+    g.set_seeds([seed])
+    g.run(steps, mcfg.timestep)
+    np.testing.assert_array_equal(pos, g.get_positions())
+    assert tail[6] == pytest.approx(g.compute_energy() / md.n, rel=1e-12)
+    g.close()
