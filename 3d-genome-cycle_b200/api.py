@@ -118,6 +118,11 @@ SYMBOLS = [
     ("gc_decomp_owned", C.c_int, [_P, C.c_void_p]),
     ("gc_decomp_host_advance", C.c_int, [_P, C.c_int64]),
     ("gc_decomp_set_owned_bound", C.c_int, [_P, C.c_int32]),
+    ("gc_decomp_recv_buffers", C.c_int, [_P, C.POINTER(C.c_void_p)]),
+    ("gc_decomp_peer_export", C.c_int, [_P, C.c_void_p]),
+    ("gc_decomp_peer_attach_ipc", C.c_int, [_P, C.c_void_p, C.c_void_p]),
+    ("gc_decomp_peer_attach", C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("gc_decomp_peer_detach", C.c_int, [_P]),
     ("gc_decomp_step_compute", C.c_int, [_P]),
     ("gc_decomp_step_commit", C.c_int, [_P]),
     ("gc_transition_interphase", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _ip, _ip, C.c_int32, _ip, C.c_int32]),
@@ -514,6 +519,32 @@ class System:
 
     def decomp_set_owned_bound(self, beads):
         self._ck(self.lib.gc_decomp_set_owned_bound(self._h, int(beads)))
+
+    def decomp_recv_buffers(self):
+        """Device addresses of recv_lo[0], recv_lo[1], recv_hi[0], recv_hi[1]."""
+        out = (C.c_void_p * 4)()
+        self._ck(self.lib.gc_decomp_recv_buffers(self._h, out))
+        return [out[k] for k in range(4)]
+
+    def decomp_peer_export(self):
+        """4 CUDA IPC handles (256 bytes) of this rank's receive buffers."""
+        blob = (C.c_ubyte * 256)()
+        self._ck(self.lib.gc_decomp_peer_export(self._h, blob))
+        return bytes(blob)
+
+    def decomp_peer_attach_ipc(self, lower_blob, upper_blob):
+        lo = C.create_string_buffer(lower_blob, 256) if lower_blob else None
+        hi = C.create_string_buffer(upper_blob, 256) if upper_blob else None
+        self._ck(self.lib.gc_decomp_peer_attach_ipc(self._h, lo, hi))
+
+    def decomp_peer_attach(self, lower=None, upper=None):
+        """Same-process neighbours: `lower` / `upper` = their decomp_recv_buffers()."""
+        lo = (lower[2], lower[3]) if lower else (None, None)
+        hi = (upper[0], upper[1]) if upper else (None, None)
+        self._ck(self.lib.gc_decomp_peer_attach(self._h, lo[0], lo[1], hi[0], hi[1]))
+
+    def decomp_peer_detach(self):
+        self._ck(self.lib.gc_decomp_peer_detach(self._h))
 
     def decomp_host_advance(self, steps):
         self._ck(self.lib.gc_decomp_host_advance(self._h, int(steps)))

@@ -56,6 +56,7 @@ struct gc_ctx {
 
     // device allocations (freed in gc_destroy)
     std::vector<void *> allocs;
+    std::vector<void *> ipc_mapped;          // peer buffers opened with cudaIpcOpenMemHandle
     float *d_mob = nullptr;
     float2 *d_ab = nullptr;
     int *d_flags = nullptr, *d_bond_off = nullptr, *d_triple_off = nullptr, *d_tether_off = nullptr;
@@ -360,6 +361,7 @@ int gc_destroy(gc_ctx *ctx)
     for (auto &k : ctx->prof) {
         for (cudaEvent_t e : k.ev) cudaEventDestroy(e);
     }
+    for (void *m : ctx->ipc_mapped) cudaIpcCloseMemHandle(m);
     for (void *p : ctx->allocs) cudaFree(p);
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->copy_event) cudaEventDestroy(ctx->copy_event);
@@ -1980,44 +1982,58 @@ int gc_launch_count(gc_ctx *ctx, int64_t *out)
 // ---------------------------------------------------------------------------
 namespace {
 
+void decomp_peer_close(gc_ctx *ctx)
+{
+    Params &P = ctx->hp;
+    for (void *m : ctx->ipc_mapped) cudaIpcCloseMemHandle(m);
+    ctx->ipc_mapped.clear();
+    for (int b = 0; b < 2; b++) P.dpeer_lo[b] = P.dpeer_hi[b] = nullptr;
+    if (P.dpeer) ctx->params_dirty = true;
+    P.dpeer = 0;
+}
+
 void decomp_release(gc_ctx *ctx)
 {
     Params &P = ctx->hp;
+    decomp_peer_close(ctx);
     if (P.dstamp) dev_free(ctx, P.dstamp);
     if (P.dsend_lo) dev_free(ctx, P.dsend_lo);
     if (P.dsend_hi) dev_free(ctx, P.dsend_hi);
-    if (P.drecv_lo) dev_free(ctx, const_cast<float4 *>(P.drecv_lo));
-    if (P.drecv_hi) dev_free(ctx, const_cast<float4 *>(P.drecv_hi));
+    for (int b = 0; b < 2; b++) {
+        if (P.drecv_lo[b]) dev_free(ctx, const_cast<float4 *>(P.drecv_lo[b]));
+        if (P.drecv_hi[b]) dev_free(ctx, const_cast<float4 *>(P.drecv_hi[b]));
+        P.drecv_lo[b] = P.drecv_hi[b] = nullptr;
+    }
     if (P.dhdr) dev_free(ctx, P.dhdr);
     if (P.dhdr_all) dev_free(ctx, const_cast<double *>(P.dhdr_all));
     P.dstamp = nullptr;
     P.dsend_lo = P.dsend_hi = nullptr;
-    P.drecv_lo = P.drecv_hi = nullptr;
     P.dhdr = nullptr;
     P.dhdr_all = nullptr;
     P.decomp = 0;
     ctx->params_dirty = true;
 }
 
+// two send buffers (in peer mode only their counters are used) and 2 x 2 receive buffers
 int decomp_alloc_halo(gc_ctx *ctx, int cap)
 {
     Params &P = ctx->hp;
-    float4 *b[4] = {nullptr, nullptr, nullptr, nullptr};
-    for (int k = 0; k < 4; k++) {
+    if (P.dpeer) return fail(ctx, GC_ERR_STATE, "detach the peer buffers before resizing (gc_decomp_peer_detach)");
+    float4 *b[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    for (int k = 0; k < 6; k++) {
         int rc = dev_alloc(ctx, &b[k], (size_t) cap + 1);
         if (rc) return rc;
-        GC_CUDA(ctx, cudaMemsetAsync(b[k], 0, ((size_t) cap + 1) * sizeof(float4), ctx->stream));
     }
     // the received halos are part of the next step's work list (decomp_current_bead): carry
     // them over when the buffers are resized mid-run
-    const float4 *old_recv[2] = {P.drecv_lo, P.drecv_hi};
-    for (int k = 0; k < 2; k++) {
+    const float4 *old_recv[4] = {P.drecv_lo[0], P.drecv_lo[1], P.drecv_hi[0], P.drecv_hi[1]};
+    for (int k = 0; k < 4; k++) {
         if (!old_recv[k]) continue;
         int count = 0;
         GC_CUDA(ctx, cudaMemcpyAsync(&count, old_recv[k], sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         if (count > cap) {
-            for (int j = 0; j < 4; j++) dev_free(ctx, b[j]);
+            for (int j = 0; j < 6; j++) dev_free(ctx, b[j]);
             return fail(ctx, GC_ERR_CAPACITY, "halo capacity %d is below the %d beads just received", cap, count);
         }
         GC_CUDA(ctx, cudaMemcpyAsync(b[2 + k], old_recv[k], ((size_t) count + 1) * sizeof(float4),
@@ -2026,12 +2042,15 @@ int decomp_alloc_halo(gc_ctx *ctx, int cap)
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (P.dsend_lo) dev_free(ctx, P.dsend_lo);
     if (P.dsend_hi) dev_free(ctx, P.dsend_hi);
-    if (P.drecv_lo) dev_free(ctx, const_cast<float4 *>(P.drecv_lo));
-    if (P.drecv_hi) dev_free(ctx, const_cast<float4 *>(P.drecv_hi));
+    for (int k = 0; k < 4; k++) {
+        if (old_recv[k]) dev_free(ctx, const_cast<float4 *>(old_recv[k]));
+    }
     P.dsend_lo = b[0];
     P.dsend_hi = b[1];
-    P.drecv_lo = b[2];
-    P.drecv_hi = b[3];
+    P.drecv_lo[0] = b[2];
+    P.drecv_lo[1] = b[3];
+    P.drecv_hi[0] = b[4];
+    P.drecv_hi[1] = b[5];
     P.dcap = cap;
     ctx->params_dirty = true;
     return GC_OK;
@@ -2103,11 +2122,89 @@ int gc_decomp_buffers(gc_ctx *ctx, void **send_lo, void **send_hi, void **recv_l
     if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
     *send_lo = P.dsend_lo;
     *send_hi = P.dsend_hi;
-    *recv_lo = const_cast<float4 *>(P.drecv_lo);
-    *recv_hi = const_cast<float4 *>(P.drecv_hi);
+    *recv_lo = const_cast<float4 *>(P.drecv_lo[0]);
+    *recv_hi = const_cast<float4 *>(P.drecv_hi[0]);
     *header = P.dhdr;
     *headers_all = const_cast<double *>(P.dhdr_all);
     *halo_elems = (size_t) P.dcap + 1;
+    return GC_OK;
+}
+
+// ---- peer mode: neighbours write the halo straight into this rank's receive buffers ------
+int gc_decomp_recv_buffers(gc_ctx *ctx, void **out4)
+{
+    GC_CHECK_CTX(ctx);
+    const Params &P = ctx->hp;
+    if (!out4) return fail(ctx, GC_ERR_INVALID, "bad args");
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    out4[0] = const_cast<float4 *>(P.drecv_lo[0]);
+    out4[1] = const_cast<float4 *>(P.drecv_lo[1]);
+    out4[2] = const_cast<float4 *>(P.drecv_hi[0]);
+    out4[3] = const_cast<float4 *>(P.drecv_hi[1]);
+    return GC_OK;
+}
+
+int gc_decomp_peer_export(gc_ctx *ctx, void *blob)
+{
+    GC_CHECK_CTX(ctx);
+    static_assert(sizeof(cudaIpcMemHandle_t) == GC_DECOMP_IPC_HANDLE_BYTES, "IPC handle size");
+    void *buf[4];
+    int rc = gc_decomp_recv_buffers(ctx, buf);
+    if (rc) return rc;
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 4; k++) {
+        cudaIpcMemHandle_t h;
+        GC_CUDA(ctx, cudaIpcGetMemHandle(&h, buf[k]));
+        memcpy((char *) blob + (size_t) k * sizeof(h), &h, sizeof(h));
+    }
+    return GC_OK;
+}
+
+int gc_decomp_peer_attach(gc_ctx *ctx, void *lower_recv_hi0, void *lower_recv_hi1, void *upper_recv_lo0,
+                          void *upper_recv_lo1)
+{
+    GC_CHECK_CTX(ctx);
+    Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    if ((P.drank > 0 && (!lower_recv_hi0 || !lower_recv_hi1)) ||
+        (P.drank + 1 < P.dworld && (!upper_recv_lo0 || !upper_recv_lo1))) {
+        return fail(ctx, GC_ERR_INVALID, "a neighbour's receive buffers are missing");
+    }
+    P.dpeer_lo[0] = (float4 *) lower_recv_hi0;
+    P.dpeer_lo[1] = (float4 *) lower_recv_hi1;
+    P.dpeer_hi[0] = (float4 *) upper_recv_lo0;
+    P.dpeer_hi[1] = (float4 *) upper_recv_lo1;
+    P.dpeer = 1;
+    ctx->params_dirty = true;
+    return GC_OK;
+}
+
+int gc_decomp_peer_attach_ipc(gc_ctx *ctx, const void *lower_blob, const void *upper_blob)
+{
+    GC_CHECK_CTX(ctx);
+    Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    decomp_peer_close(ctx);
+    void *ptr[4] = {nullptr, nullptr, nullptr, nullptr};   // lower hi[0], hi[1], upper lo[0], lo[1]
+    for (int k = 0; k < 4; k++) {
+        const bool lower = k < 2;
+        if (lower ? P.drank == 0 : P.drank + 1 >= P.dworld) continue;
+        const void *blob = lower ? lower_blob : upper_blob;
+        if (!blob) return fail(ctx, GC_ERR_INVALID, "a neighbour's export blob is missing");
+        // blob = recv_lo[0], recv_lo[1], recv_hi[0], recv_hi[1] of that rank
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char *) blob + (size_t) (lower ? 2 + k : k - 2) * sizeof(h), sizeof(h));
+        GC_CUDA(ctx, cudaIpcOpenMemHandle(&ptr[k], h, cudaIpcMemLazyEnablePeerAccess));
+        ctx->ipc_mapped.push_back(ptr[k]);
+    }
+    return gc_decomp_peer_attach(ctx, ptr[0], ptr[1], ptr[2], ptr[3]);
+}
+
+int gc_decomp_peer_detach(gc_ctx *ctx)
+{
+    GC_CHECK_CTX(ctx);
+    GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    decomp_peer_close(ctx);
     return GC_OK;
 }
 
@@ -2124,15 +2221,22 @@ int gc_decomp_step_compute(gc_ctx *ctx)
     launch_pair(ctx, 0u, 1);
     LAUNCH(ctx, k_finish<STEP_FUSED>, dim3((P.down_bound + BS - 1) / BS, 1), BS, ctx->hp, 0u, 1);
     LAUNCH(ctx, k_decomp_header, 1, 32, ctx->hp);
+    if (P.dpeer) {
+        // the halo leaves now, straight into the neighbours' buffers; the header all-gather
+        // the caller runs next is the step's only collective
+        LAUNCH(ctx, k_decomp_pack, std::min((P.down_bound + 255) / 256, 148 * 8), 256, ctx->hp);
+        LAUNCH(ctx, k_decomp_publish, 1, 32, ctx->hp);
+    }
     return GC_OK;
 }
 
 int gc_decomp_step_pack(gc_ctx *ctx)
 {
     GC_CHECK_CTX(ctx);
-    if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
+    const Params &P = ctx->hp;
+    if (!P.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
     LAUNCH(ctx, k_finalize_step, 1, 32, ctx->hp, 0);
-    LAUNCH(ctx, k_decomp_pack, std::min((ctx->n + 255) / 256, 148 * 8), 256, ctx->hp);
+    if (!P.dpeer) LAUNCH(ctx, k_decomp_pack, std::min((P.down_bound + 255) / 256, 148 * 8), 256, ctx->hp);
     ctx->run_step++;
     ctx->parity ^= 1;
     return GC_OK;
@@ -2142,8 +2246,7 @@ int gc_decomp_step_commit(gc_ctx *ctx)
 {
     GC_CHECK_CTX(ctx);
     if (!ctx->hp.decomp) return fail(ctx, GC_ERR_STATE, "gc_decomp_configure has not been called");
-    const int blocks = std::max(1, std::min((ctx->hp.dcap + 255) / 256, 148 * 4));
-    LAUNCH(ctx, k_decomp_unpack, dim3(blocks, 2), 256, ctx->hp);
+    // nothing to launch: the next step's k_count takes the received beads in on its way
     return GC_OK;
 }
 
@@ -2164,6 +2267,8 @@ int gc_decomp_owned(gc_ctx *ctx, uint8_t *mask)
     unsigned char *d = nullptr;
     int rc = dev_alloc(ctx, &d, (size_t) ctx->n);
     if (rc) return rc;
+    // halos received since the last step are taken in first
+    k_decomp_unpack<<<dim3(std::max(1, std::min((ctx->hp.dcap + 255) / 256, 148 * 4)), 2), 256, 0, ctx->stream>>>(ctx->hp);
     k_decomp_owned<<<(ctx->n + 255) / 256, 256, 0, ctx->stream>>>(ctx->hp, d);
     cudaError_t e = cudaMemcpyAsync(mask, d, (size_t) ctx->n, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);

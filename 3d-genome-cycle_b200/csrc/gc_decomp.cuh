@@ -61,41 +61,62 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
     st.dprev_lo = start[st.zown_lo * dxy];
     st.dprev_hi = start[st.zown_hi * dxy];
     st.dfull = 0;
+    // ... and the grid it was moved under (peer mode ships under this grid)
+    st.dold_oz = st.origin[2];
+    st.dold_inv = st.inv_cell;
+    st.dold_gdimz = st.gdimz;
+    st.dold_z0 = st.zoff + st.zown_lo;
+    st.dold_z1 = st.zoff + st.zown_hi;
     // the send buffers restart empty
     reinterpret_cast<int *>(P.dsend_lo)[0] = 0;
     reinterpret_cast<int *>(P.dsend_hi)[0] = 0;
 }
 
-// after the callback body planned the next grid: ship the moved beads the neighbours need
+// Ships the moved beads the neighbours need.
+//   NCCL mode: after the callback body planned the next grid; beads within dhalo layers of a
+//     neighbour's NEW slab go to the send buffers, which the caller exchanges.
+//   Peer mode: right after k_finish, under the grid of the step just taken with one layer
+//     more (the next k_count checks the set against the new grid), and straight into the
+//     neighbour's receive buffer of this step's parity over NVLink; k_decomp_publish then
+//     writes the counts.  The header all-gather that follows is the step's only collective
+//     and orders these writes before the neighbour reads them.
 __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Params P)
 {
     GC_PDL_ENTRY();
     RepState &st = P.st[0];
-    __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2 in the NEW grid
+    __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2
     if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P.drank - 1 + threadIdx.x, P.dworld, st.gdimz, P.cells_per_cut);
     __syncthreads();
-    const int z0 = zs[1], z1 = zs[2];
     const int lane = threadIdx.x & 31;
-    // the beads this rank moved in the step just taken: k_finish left them in the slot order
-    // of that step, in the sorted buffer of the parity that is current now
+    const int peer = P.dpeer;
+    // peer mode runs before the callback flipped the parity and advanced the step
+    const float4 *__restrict__ moved = P.spos[peer ? st.parity ^ 1 : st.parity] + st.dprev_lo;
+    const int reach = P.dhalo + (peer ? 1 : 0);
+    const int z0 = peer ? st.dold_z0 : zs[1], z1 = peer ? st.dold_z1 : zs[2];
+    const int wb = (int) (st.step & 1);
+    float4 *out_lo = peer ? P.dpeer_lo[wb] : P.dsend_lo;
+    float4 *out_hi = peer ? P.dpeer_hi[wb] : P.dsend_hi;
+    // the beads this rank moved in the step just taken, left in slot order by k_finish
     const int nw = st.dprev_hi - st.dprev_lo;
     const int nw_pad = (nw + 31) & ~31;             // whole warps: the appends below are warp-aggregated
     for (int w = blockIdx.x * 256 + threadIdx.x; w < nw_pad; w += gridDim.x * 256) {
         const bool live = w < nw;
         float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live) x = P.spos[st.parity][st.dprev_lo + w];   // new position, bead index in .w
+        if (live) x = moved[w];                     // new position, bead index in .w
         const int layer = cell_layer(st, x.z, P.cells_per_cut);
-        // a bead that jumped past a neighbour's whole slab would be lost
-        if (live && (layer < zs[0] || layer >= zs[3])) atomicExch(&st.error, 3);
-        const bool to_lo = live && P.drank > 0 && layer < z0 + P.dhalo;
-        const bool to_hi = live && P.drank + 1 < P.dworld && layer >= z1 - P.dhalo;
+        // a bead that jumped past a neighbour's whole slab would be lost (peer mode: k_count)
+        if (!peer && live && (layer < zs[0] || layer >= zs[3])) atomicExch(&st.error, 3);
+        const bool to_lo = live && P.drank > 0 && layer < z0 + reach;
+        const bool to_hi = live && P.drank + 1 < P.dworld && layer >= z1 - reach;
 #pragma unroll
         for (int side = 0; side < 2; side++) {
             const unsigned m = __ballot_sync(0xffffffffu, side ? to_hi : to_lo);
             if (!m) continue;
-            float4 *buf = side ? P.dsend_hi : P.dsend_lo;
+            // the count lives in the LOCAL send buffer in both modes
+            int *counter = reinterpret_cast<int *>(side ? P.dsend_hi : P.dsend_lo);
+            float4 *buf = side ? out_hi : out_lo;
             int base = 0;
-            if (lane == __ffs(m) - 1) base = atomicAdd(reinterpret_cast<int *>(buf), __popc(m));
+            if (lane == __ffs(m) - 1) base = atomicAdd(counter, __popc(m));
             base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
             if (side ? to_hi : to_lo) {
                 const int k = base + __popc(m & ((1u << lane) - 1u));
@@ -105,16 +126,30 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
     }
 }
 
-// after the neighbour exchange: received beads by bead index, stamped current
+// peer mode, after k_decomp_pack: the bead counts into the neighbours' buffers
+__global__ void k_decomp_publish(const __grid_constant__ Params P)
+{
+    GC_PDL_ENTRY();
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const RepState &st = P.st[0];
+    const int wb = (int) (st.step & 1);
+    if (P.drank > 0) reinterpret_cast<int *>(P.dpeer_lo[wb])[0] = min(reinterpret_cast<const int *>(P.dsend_lo)[0], P.dcap);
+    if (P.drank + 1 < P.dworld) reinterpret_cast<int *>(P.dpeer_hi[wb])[0] = min(reinterpret_cast<const int *>(P.dsend_hi)[0], P.dcap);
+}
+
+// Received beads by bead index, stamped current.  The next k_count does this on its way;
+// this kernel serves the queries between two steps (gc_decomp_owned).
 __global__ void __launch_bounds__(256) k_decomp_unpack(const __grid_constant__ Params P)
 {
     GC_PDL_ENTRY();
     RepState &st = P.st[0];
     float4 *__restrict__ pos = P.pos[st.parity];
     const int side = blockIdx.y;
+    if (st.dfull) return;
     if (side == 0 && P.drank == 0) return;
     if (side == 1 && P.drank + 1 >= P.dworld) return;
-    const float4 *buf = side == 0 ? P.drecv_lo : P.drecv_hi;
+    const int rb = decomp_recv_index(P, st);
+    const float4 *buf = side == 0 ? P.drecv_lo[rb] : P.drecv_hi[rb];
     const int count = min(reinterpret_cast<const int *>(buf)[0], P.dcap);
     for (int k = blockIdx.x * 256 + threadIdx.x; k < count; k += gridDim.x * 256) {
         const float4 v = buf[1 + k];

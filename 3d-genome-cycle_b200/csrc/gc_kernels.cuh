@@ -231,18 +231,25 @@ __global__ void k_bbox(const __grid_constant__ Params P)
 
 // Decomposed runs: the beads current on this rank, enumerated without touching the other
 // N - N / ranks beads (RepState::dfull / dprev_*).
+__device__ __forceinline__ int decomp_recv_index(const Params &P, const RepState &st)
+{
+    return P.dpeer ? (int) ((st.step + 1) & 1) : 0;      // written during step st.step - 1
+}
+
 __device__ __forceinline__ int decomp_current_count(const Params &P, const RepState &st)
 {
     if (st.dfull) return P.n;
+    const int rb = decomp_recv_index(P, st);
     int w = st.dprev_hi - st.dprev_lo;
-    if (P.drank > 0) w += min(reinterpret_cast<const int *>(P.drecv_lo)[0], P.dcap);
-    if (P.drank + 1 < P.dworld) w += min(reinterpret_cast<const int *>(P.drecv_hi)[0], P.dcap);
+    if (P.drank > 0) w += min(reinterpret_cast<const int *>(P.drecv_lo[rb])[0], P.dcap);
+    if (P.drank + 1 < P.dworld) w += min(reinterpret_cast<const int *>(P.drecv_hi[rb])[0], P.dcap);
     return w;
 }
 
-// (x, y, z, bead index bits) of work item w
-__device__ __forceinline__ float4 decomp_current_bead(const Params &P, const RepState &st, int w)
+// (x, y, z, bead index bits) of work item w; *received = it came in a halo buffer
+__device__ __forceinline__ float4 decomp_current_bead(const Params &P, const RepState &st, int w, bool *received)
 {
+    *received = false;
     if (st.dfull) {
         float4 p = P.pos[st.parity][w];
         p.w = __int_as_float(w);
@@ -252,10 +259,12 @@ __device__ __forceinline__ float4 decomp_current_bead(const Params &P, const Rep
     // k_finish left the moved beads in the slot order of the step just taken, in the sorted
     // buffer of the parity that is current now (this step's k_gather overwrites it later)
     if (w < na) return P.spos[st.parity][st.dprev_lo + w];
+    *received = true;
     w -= na;
-    const int nlo = P.drank > 0 ? min(reinterpret_cast<const int *>(P.drecv_lo)[0], P.dcap) : 0;
-    if (w < nlo) return P.drecv_lo[1 + w];
-    return P.drecv_hi[1 + w - nlo];
+    const int rb = decomp_recv_index(P, st);
+    const int nlo = P.drank > 0 ? min(reinterpret_cast<const int *>(P.drecv_lo[rb])[0], P.dcap) : 0;
+    if (w < nlo) return P.drecv_lo[rb][1 + w];
+    return P.drecv_hi[rb][1 + w - nlo];
 }
 
 __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
@@ -274,10 +283,32 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
         const int stride = gridDim.x * blockDim.x;
         for (int k = i + stride; k < P.scan_blocks; k += stride) P.scan_status[k] = 0ull;
         const int nw = decomp_current_count(P, st);
+        const int h = P.cells_per_cut;
+        __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2
+        if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P.drank - 1 + threadIdx.x, P.dworld, st.gdimz, h);
+        __syncthreads();
         for (int w = i; w < nw; w += stride) {
-            const float4 p = decomp_current_bead(P, st, w);
+            bool received;
+            const float4 p = decomp_current_bead(P, st, w, &received);
             const int b = __float_as_int(p.w);
-            const int c = cell_index(st, p, P.cells_per_cut);
+            if (received) {
+                // a halo copy: position by bead index (bonded partners are looked up there),
+                // stamped current
+                P.pos[st.parity][b] = make_float4(p.x, p.y, p.z, 0.0f);
+                P.dstamp[b] = (int) st.step;
+            } else if (P.dpeer && !st.dfull) {
+                // moved here in the last step and shipped under THAT step's grid: everything a
+                // neighbour needs under the new grid must have been in the shipped set
+                const int ln = cell_layer(st, p.z, h);
+                const int lo_ = cell_coord(p.z, st.dold_oz, st.dold_inv, st.dold_gdimz, h);
+                const bool sent_lo = lo_ < st.dold_z0 + P.dhalo + 1, sent_hi = lo_ >= st.dold_z1 - P.dhalo - 1;
+                const bool need_lo = P.drank > 0 && ln < zs[1] + P.dhalo;
+                const bool need_hi = P.drank + 1 < P.dworld && ln >= zs[2] - P.dhalo;
+                const bool lost = (P.drank > 1 && ln < zs[0] + P.dhalo) ||
+                                  (P.drank + 2 < P.dworld && ln >= zs[3] - P.dhalo);
+                if ((need_lo && !sent_lo) || (need_hi && !sent_hi) || lost) atomicExch(&P.st[r].error, 3);
+            }
+            const int c = cell_index(st, p, h);
             P.cell_of[b] = c;
             if (c >= 0) atomicAdd(&P.cell_count[c], 1);
         }
@@ -406,7 +437,8 @@ __global__ void __launch_bounds__(256) k_fill(const __grid_constant__ Params P)
     if (P.decomp) {
         const int nw = decomp_current_count(P, st);
         for (int w = i; w < nw; w += gridDim.x * blockDim.x) {
-            const int b = __float_as_int(decomp_current_bead(P, st, w).w);
+            bool received;
+            const int b = __float_as_int(decomp_current_bead(P, st, w, &received).w);
             const int c = P.cell_of[b];
             if (c < 0) continue;
             P.members[P.cell_start[c] + atomicAdd(&P.cell_count[c], 1)] = b;

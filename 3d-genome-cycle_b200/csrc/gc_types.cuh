@@ -176,6 +176,11 @@ struct RepState {
     // slots [dprev_lo, dprev_hi) it moved in the last step (bead index in spos[].w) plus the
     // two received halo buffers; dfull = 1: all N beads (after gc_run(restart = 1))
     int dfull, dprev_lo, dprev_hi;
+    // peer mode packs under the grid of the step just taken (one layer more than dhalo, so that
+    // the header all-gather is the only collective of a step); the next cell-list build
+    // checks, under the new grid, that everything a neighbour needs was in that set
+    float dold_oz, dold_inv;
+    int dold_gdimz, dold_z0, dold_z1;
     StepConst sc;
 };
 
@@ -230,7 +235,12 @@ struct Params {
     int down_bound;                // bound on the beads a rank owns (sizes k_finish's grid)
     int *dstamp;                   // [N] step at which pos[] of a bead was last written on this rank
     float4 *dsend_lo, *dsend_hi;   // [dcap + 1] (x, y, z, bead) for rank - 1 / rank + 1; [0].x = count bits
-    const float4 *drecv_lo, *drecv_hi;   // the same, received from rank - 1 / rank + 1
+    // the same, received from rank - 1 / rank + 1.  Peer mode (dpeer = 1) double-buffers them by
+    // step parity and the neighbours write them DIRECTLY over NVLink: dpeer_lo[b] is rank - 1's
+    // drecv_hi[b], dpeer_hi[b] is rank + 1's drecv_lo[b] (peer-mapped)
+    const float4 *drecv_lo[2], *drecv_hi[2];
+    float4 *dpeer_lo[2], *dpeer_hi[2];
+    int dpeer;
     double *dhdr;                  // [16] this rank's share of the per-step reductions
     const double *dhdr_all;        // [dworld][16] every rank's header, gathered
     const float *noise;            // injected normals [R][steps][N][3] or null

@@ -36,10 +36,15 @@ class DecomposedRun:
     """Drives gc_decomp_step_compute -> header all-gather -> gc_decomp_step_pack ->
     neighbour send/recv -> gc_decomp_step_commit on the context's own stream."""
 
-    scheme = "z-slabs of the cell grid + halo exchange with the two neighbouring ranks"
+    @property
+    def scheme(self):
+        how = ("packed straight into the neighbours' buffers over NVLink peer memory (CUDA IPC); one header "
+               "all-gather per step" if self.peer else "header all-gather + NCCL send/recv with the two neighbours")
+        return "z-slabs of the cell grid + halo exchange: " + how
 
     def __init__(self, system, rank: int, world: int, device: int = 0, group=None,
-                 halo_layers: int | None = None, halo_capacity: int = 0, graph_steps: int = 0):
+                 halo_layers: int | None = None, halo_capacity: int = 0, graph_steps: int = 0,
+                 peer: bool = False):
         import torch
         self.sys, self.rank, self.world, self.group = system, rank, world, group
         self.device = device
@@ -53,7 +58,26 @@ class DecomposedRun:
             if halo_layers is not None or halo_capacity:
                 system.decomp_set_halo(self.halo_layers, halo_capacity)
             self.buf = system.decomp_buffers(device)
+        self.peer = bool(peer) and world > 1
+        if self.peer:
+            self._attach_peers()
         self.stream = torch.cuda.ExternalStream(system.stream(), device=device)
+
+    def _attach_peers(self):
+        """Peer mode: every rank maps its neighbours' receive buffers (CUDA IPC) and packs the
+        halo straight into them over NVLink; the header all-gather is then the only
+        collective of a step."""
+        import torch.distributed as dist
+        blobs = [None] * self.world
+        dist.all_gather_object(blobs, self.sys.decomp_peer_export(), group=self.group)
+        self.sys.decomp_peer_attach_ipc(blobs[self.rank - 1] if self.rank > 0 else None,
+                                        blobs[self.rank + 1] if self.rank + 1 < self.world else None)
+        dist.barrier(group=self.group)
+
+    def _detach_peers(self):
+        import torch.distributed as dist
+        self.sys.decomp_peer_detach()
+        dist.barrier(group=self.group)          # nobody resizes before everybody has let go
 
     def begin(self, timestep, temperature=1.0):
         """Temperature / timestep, restart, first grid plan (gc_run with 0 steps); every rank
@@ -74,7 +98,12 @@ class DecomposedRun:
                          device=f"cuda:{self.device}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         cap = int(slack * int(t[0].item())) + floor
+        self.invalidate_graph()
+        if self.peer:
+            self._detach_peers()
         self.sys.decomp_set_halo(self.halo_layers, cap)
+        if self.peer:
+            self._attach_peers()
         self.sys.decomp_set_owned_bound(int(slack * int(t[1].item())) + floor)
         timestep, temperature = self._run_args
         self.sys.run(0, timestep, temperature=temperature, restart=False)   # parameters only
@@ -88,8 +117,11 @@ class DecomposedRun:
         (whole buffers travel; the bead count rides in their first element)."""
         if self.world == 1:
             return 0
-        halo = self.buf["send_lo"].numel() * 4
         sides = (self.rank > 0) + (self.rank + 1 < self.world)
+        if self.peer:                       # only the packed beads cross NVLink
+            halo = 16 * sum(self.halo_counts()) + 16 * sides
+            return HEADER_DOUBLES * 8 * (self.world - 1) + halo
+        halo = self.buf["send_lo"].numel() * 4
         return HEADER_DOUBLES * 8 * (self.world - 1) + sides * halo
 
     def halo_counts(self):
@@ -146,10 +178,18 @@ class DecomposedRun:
             s.decomp_step_compute()
             dist.all_gather_into_tensor(b["headers_all"], b["header"], group=self.group)
             s.decomp_step_pack()
-            ops = [dist.P2POp(op, t, self._peer(peer), group=self.group) for op, t, peer in ops_template]
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+            if not self.peer:
+                ops = [dist.P2POp(op, t, self._peer(peer), group=self.group) for op, t, peer in ops_template]
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
             s.decomp_step_commit()
+
+    def close(self):
+        """Before the context or the process group goes away."""
+        self.invalidate_graph()
+        if self.peer:
+            self._detach_peers()
+            self.peer = False
 
     def timed_phases(self, steps=20):
         """Eager steps with CUDA events between the phases: mean ms of (compute, header
@@ -217,7 +257,7 @@ class LocalExchange:
     """`world` contexts on ONE device standing in for `world` ranks: the collectives are
     device-to-device copies.  Used by the single-GPU parity tests."""
 
-    def __init__(self, systems, device=0, halo_layers=None, halo_capacity=0):
+    def __init__(self, systems, device=0, halo_layers=None, halo_capacity=0, peer=False):
         import torch
         self.systems = systems
         self.world = len(systems)
@@ -228,6 +268,14 @@ class LocalExchange:
         self.device = device
         self.bufs = [s.decomp_buffers(device) for s in systems]
         self.torch = torch
+        self.peer = bool(peer)
+        if self.peer:
+            self._attach()
+
+    def _attach(self):
+        recv = [s.decomp_recv_buffers() for s in self.systems]
+        for k, s in enumerate(self.systems):
+            s.decomp_peer_attach(recv[k - 1] if k > 0 else None, recv[k + 1] if k + 1 < self.world else None)
 
     def begin(self, timestep, temperature=1.0):
         for s in self.systems:
@@ -248,10 +296,11 @@ class LocalExchange:
                 s.decomp_step_pack()
             for s in self.systems:
                 s.synchronize()
-            for k in range(self.world - 1):
-                self.bufs[k + 1]["recv_lo"].copy_(self.bufs[k]["send_hi"])
-                self.bufs[k]["recv_hi"].copy_(self.bufs[k + 1]["send_lo"])
-            self.torch.cuda.synchronize()
+            if not self.peer:
+                for k in range(self.world - 1):
+                    self.bufs[k + 1]["recv_lo"].copy_(self.bufs[k]["send_hi"])
+                    self.bufs[k]["recv_hi"].copy_(self.bufs[k + 1]["send_lo"])
+                self.torch.cuda.synchronize()
             for s in self.systems:
                 s.decomp_step_commit()
 
@@ -259,7 +308,13 @@ class LocalExchange:
         """Resizes every rank's halo buffers between two steps."""
         for s in self.systems:
             s.synchronize()
+            if self.peer:
+                s.decomp_peer_detach()
+        for s in self.systems:
             s.decomp_set_halo(layers, capacity)
+        if self.peer:
+            self._attach()
+        for s in self.systems:
             s.run(0, timestep, temperature=temperature, restart=False)   # parameters only
         self.bufs = [s.decomp_buffers(self.device) for s in self.systems]
 

@@ -330,6 +330,29 @@ int gc_decomp_buffers(gc_ctx *ctx, void **send_lo, void **send_hi, void **recv_l
 int gc_decomp_step_compute(gc_ctx *ctx);
 int gc_decomp_step_pack(gc_ctx *ctx);
 int gc_decomp_step_commit(gc_ctx *ctx);
+
+/* PEER MODE: the halo leaves inside gc_decomp_step_compute, written by the pack kernel
+   straight into the neighbours' receive buffers over NVLink (peer-mapped memory), so the
+   header all-gather is the ONLY collective of a step and orders those writes before the
+   neighbour reads them:
+       gc_decomp_step_compute -> all-gather(header) -> gc_decomp_step_pack [-> _commit: no-op]
+   The receive buffers are double-buffered by step parity.  The halo is chosen under the grid
+   of the step just taken with one layer more than `layers`; the next step checks under the
+   new grid that nothing a neighbour needs was left out (GC_ERR_STATE otherwise).
+   Set-up, before gc_run(restart = 1): every rank exports its four receive buffers
+   (gc_decomp_peer_export: 4 CUDA IPC handles = 4 x 64 bytes: recv_lo[0], recv_lo[1],
+   recv_hi[0], recv_hi[1]), the blobs travel by any means, and each rank attaches the blob of
+   rank - 1 and of rank + 1 (NULL where there is none).  Ranks that live in one process attach
+   raw pointers instead (gc_decomp_recv_buffers of the neighbours -> gc_decomp_peer_attach).
+   gc_decomp_peer_detach closes the mappings (before a neighbour resizes or frees its
+   buffers) and returns to the send / receive scheme. */
+#define GC_DECOMP_IPC_HANDLE_BYTES 64
+int gc_decomp_recv_buffers(gc_ctx *ctx, void **out4);
+int gc_decomp_peer_export(gc_ctx *ctx, void *blob /* 4 x GC_DECOMP_IPC_HANDLE_BYTES */);
+int gc_decomp_peer_attach_ipc(gc_ctx *ctx, const void *lower_blob, const void *upper_blob);
+int gc_decomp_peer_attach(gc_ctx *ctx, void *lower_recv_hi0, void *lower_recv_hi1, void *upper_recv_lo0,
+                          void *upper_recv_lo1);
+int gc_decomp_peer_detach(gc_ctx *ctx);
 /* The three step calls only enqueue kernels, so a block of steps -- with the caller's
    collectives between them -- can be captured into a CUDA graph on gc_stream and replayed.
    The library keeps a host-side mirror of the step count and of the position buffer in use:

@@ -71,7 +71,8 @@ def _interphase_rank(d, cfg, x, seed=77):
 
 
 @pytest.mark.gpu
-def test_decomposed_trajectory_is_bit_identical():
+@pytest.mark.parametrize("peer", [False, True])
+def test_decomposed_trajectory_is_bit_identical(peer):
     """A whole (scaled-down) nucleus on two ranks: chains, nucleolar bonds, the nucleolar
     droplet (whose targets may not be current on a rank: they are then beyond its reach), the
     wall ODE.  The grid has about ten layers, so two slabs of five with a three-layer halo
@@ -85,7 +86,7 @@ def test_decomposed_trajectory_is_bit_identical():
     ref.close()
 
     ranks = [_interphase_rank(d, cfg, x) for _ in range(world)]
-    ex = decomp.LocalExchange(ranks, halo_layers=3)
+    ex = decomp.LocalExchange(ranks, halo_layers=3, peer=peer)
     ex.begin(cfg.timestep)
     ex.step(steps)
     np.testing.assert_array_equal(ex.gather_positions(), xr)
@@ -106,9 +107,11 @@ def _polymer_rank(d, x, cfg):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world", [2, 3, 8])
-def test_decomposed_200k_polymer_is_bit_identical_and_exchanges_a_surface(world):
-    """BASELINE configs[4] at a size the suite affords: 2 x 10^5 beads, 30 steps.  Bit-equal
+@pytest.mark.parametrize("world,peer", [(2, False), (3, True), (8, False), (8, True)])
+def test_decomposed_200k_polymer_is_bit_identical_and_exchanges_a_surface(world, peer):
+    """peer = True: the pack kernel writes straight into the neighbours' receive buffers (on one
+    device here, over NVLink peer memory between processes) under the old grid + one layer.
+    BASELINE configs[4] at a size the suite affords: 2 x 10^5 beads, 30 steps.  Bit-equal
     positions, every bead owned exactly once, balanced slabs, and a halo that is a surface
     term (the round-1 scheme shipped every bead to every rank)."""
     n, steps = 200_000, 30
@@ -123,7 +126,7 @@ def test_decomposed_200k_polymer_is_bit_identical_and_exchanges_a_surface(world)
 
     ranks = [_polymer_rank(d, x, cfg) for _ in range(world)]
     # the walk's bonds (0.3) span two cell edges (0.15): a three-layer position halo
-    ex = decomp.LocalExchange(ranks, halo_layers=3)
+    ex = decomp.LocalExchange(ranks, halo_layers=3, peer=peer)
     ex.begin(cfg.timestep)
     ex.step(steps // 2)
     # resizing the halo buffers mid-run keeps the halos just received
