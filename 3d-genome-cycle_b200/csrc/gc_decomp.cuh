@@ -75,8 +75,8 @@ __global__ void k_decomp_header(const __grid_constant__ Params P)
 // Ships the moved beads the neighbours need.
 //   NCCL mode: after the callback body planned the next grid; beads within dhalo layers of a
 //     neighbour's NEW slab go to the send buffers, which the caller exchanges.
-//   Peer mode: right after k_finish, under the grid of the step just taken with one layer
-//     more (the next k_count checks the set against the new grid), and straight into the
+//   Peer mode: right after k_finish, under the grid of the step just taken with
+//     GC_DECOMP_PEER_MARGIN layers more (the next k_count checks the set against the new grid), and straight into the
 //     neighbour's receive buffer of this step's parity over NVLink; k_decomp_publish then
 //     writes the counts.  The header all-gather that follows is the step's only collective
 //     and orders these writes before the neighbour reads them.
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
     const int peer = P.dpeer;
     // peer mode runs before the callback flipped the parity and advanced the step
     const float4 *__restrict__ moved = P.spos[peer ? st.parity ^ 1 : st.parity] + st.dprev_lo;
-    const int reach = P.dhalo + (peer ? 1 : 0);
+    const int reach = P.dhalo + (peer ? GC_DECOMP_PEER_MARGIN : 0);
     const int z0 = peer ? st.dold_z0 : zs[1], z1 = peer ? st.dold_z1 : zs[2];
     const int wb = (int) (st.step & 1);
     float4 *out_lo = peer ? P.dpeer_lo[wb] : P.dsend_lo;
@@ -124,6 +124,9 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
             }
         }
     }
+    // peer stores are posted writes over NVLink: every thread makes its own visible system-wide
+    // before the grid -- and with it the stream order the all-gather hangs on -- completes
+    if (peer) __threadfence_system();
 }
 
 // peer mode, after k_decomp_pack: the bead counts into the neighbours' buffers
@@ -135,6 +138,7 @@ __global__ void k_decomp_publish(const __grid_constant__ Params P)
     const int wb = (int) (st.step & 1);
     if (P.drank > 0) reinterpret_cast<int *>(P.dpeer_lo[wb])[0] = min(reinterpret_cast<const int *>(P.dsend_lo)[0], P.dcap);
     if (P.drank + 1 < P.dworld) reinterpret_cast<int *>(P.dpeer_hi[wb])[0] = min(reinterpret_cast<const int *>(P.dsend_hi)[0], P.dcap);
+    __threadfence_system();
 }
 
 // Received beads by bead index, stamped current.  The next k_count does this on its way;

@@ -301,7 +301,8 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
                 // neighbour needs under the new grid must have been in the shipped set
                 const int ln = cell_layer(st, p.z, h);
                 const int lo_ = cell_coord(p.z, st.dold_oz, st.dold_inv, st.dold_gdimz, h);
-                const bool sent_lo = lo_ < st.dold_z0 + P.dhalo + 1, sent_hi = lo_ >= st.dold_z1 - P.dhalo - 1;
+                const int reach = P.dhalo + GC_DECOMP_PEER_MARGIN;
+                const bool sent_lo = lo_ < st.dold_z0 + reach, sent_hi = lo_ >= st.dold_z1 - reach;
                 const bool need_lo = P.drank > 0 && ln < zs[1] + P.dhalo;
                 const bool need_hi = P.drank + 1 < P.dworld && ln >= zs[2] - P.dhalo;
                 const bool lost = (P.drank > 1 && ln < zs[0] + P.dhalo) ||

@@ -176,7 +176,7 @@ struct RepState {
     // slots [dprev_lo, dprev_hi) it moved in the last step (bead index in spos[].w) plus the
     // two received halo buffers; dfull = 1: all N beads (after gc_run(restart = 1))
     int dfull, dprev_lo, dprev_hi;
-    // peer mode packs under the grid of the step just taken (one layer more than dhalo, so that
+    // peer mode packs under the grid of the step just taken (GC_DECOMP_PEER_MARGIN layers more, so that
     // the header all-gather is the only collective of a step); the next cell-list build
     // checks, under the new grid, that everything a neighbour needs was in that set
     float dold_oz, dold_inv;
@@ -267,6 +267,12 @@ __device__ __forceinline__ float *unit_half(const Params &P, int r, int slot, in
     return reinterpret_cast<float *>(P.punit + (size_t) plane * P.unit_plane + (size_t) r * P.n_units +
                                      (size_t) (slot >> 1)) + (slot & 1);
 }
+
+// Peer mode of a decomposed run ships the halo under the grid of the step just taken.  Between
+// two plans a slab boundary moves by at most one layer (the grid gains or loses one) and a
+// bead's layer by at most one (its own motion plus the shift of the origin are far below a
+// cell edge), so two extra layers cover what the new grid can ask for; k_count verifies.
+constexpr int GC_DECOMP_PEER_MARGIN = 2;
 
 // Position of sorted slot s (a bead of z layer L, whose first slot is layer_start) in the
 // pair-interleaved copy.  Beads are paired RELATIVE TO THEIR LAYER -- the first bead of a

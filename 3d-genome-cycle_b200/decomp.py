@@ -216,8 +216,9 @@ class DecomposedRun:
                 if self.rank > 0:
                     ops += [dist.P2POp(dist.isend, b["send_lo"], self._peer(self.rank - 1), group=self.group),
                             dist.P2POp(dist.irecv, b["recv_lo"], self._peer(self.rank - 1), group=self.group)]
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
+                if not self.peer:
+                    for w in dist.batch_isend_irecv(ops):
+                        w.wait()
                 ev[k][4].record(self.stream)
                 s.decomp_step_commit()
                 ev[k][5].record(self.stream)

@@ -337,7 +337,7 @@ int gc_decomp_step_commit(gc_ctx *ctx);
    neighbour reads them:
        gc_decomp_step_compute -> all-gather(header) -> gc_decomp_step_pack [-> _commit: no-op]
    The receive buffers are double-buffered by step parity.  The halo is chosen under the grid
-   of the step just taken with one layer more than `layers`; the next step checks under the
+   of the step just taken with two layers more than `layers`; the next step checks under the
    new grid that nothing a neighbour needs was left out (GC_ERR_STATE otherwise).
    Set-up, before gc_run(restart = 1): every rank exports its four receive buffers
    (gc_decomp_peer_export: 4 CUDA IPC handles = 4 x 64 bytes: recv_lo[0], recv_lo[1],

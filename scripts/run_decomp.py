@@ -28,6 +28,7 @@ ap.add_argument("--check", action="store_true")
 ap.add_argument("--profile", type=int, default=0, help="per-kernel event timing over this many steps")
 ap.add_argument("--halo", type=int, default=3, help="position halo in cell layers")
 ap.add_argument("--cap-frac", type=float, default=0.0, help="halo buffer beads / (N / world); 0 = default")
+ap.add_argument("--peer", action="store_true", help="halo through NVLink peer memory (CUDA IPC)")
 ap.add_argument("--graph", type=int, default=0, help="steps per CUDA graph (0: eager)")
 ap.add_argument("--out", default="")
 a = ap.parse_args()
@@ -78,7 +79,7 @@ if world > 1:
     g = make()
     run = decomp.DecomposedRun(g, rank, world, local, halo_layers=a.halo,
                                halo_capacity=int(a.cap_frac * design.n / world),
-                               graph_steps=a.graph)
+                               graph_steps=a.graph, peer=a.peer)
     run.begin(cfg.timestep)
     run.step(a.warmup // 2)
     rep["halo_capacity_beads"] = run.tune_capacity()
@@ -120,6 +121,7 @@ if world > 1:
     run.invalidate_graph()
     if a.check:
         x_dec = run.gather_positions()
+    run.close()
     g.close()
 if rank == 0:
     g = make()
