@@ -70,9 +70,18 @@ class DecomposedRun:
         import torch.distributed as dist
         blobs = [None] * self.world
         dist.all_gather_object(blobs, self.sys.decomp_peer_export(), group=self.group)
-        self.sys.decomp_peer_attach_ipc(blobs[self.rank - 1] if self.rank > 0 else None,
-                                        blobs[self.rank + 1] if self.rank + 1 < self.world else None)
-        dist.barrier(group=self.group)
+        import torch
+        err = None
+        try:
+            self.sys.decomp_peer_attach_ipc(blobs[self.rank - 1] if self.rank > 0 else None,
+                                            blobs[self.rank + 1] if self.rank + 1 < self.world else None)
+        except Exception as ex:             # e.g. no peer access between two devices
+            err = ex
+        ok = torch.tensor([0 if err else 1], device=f"cuda:{self.device}")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)      # also the barrier
+        if int(ok.item()) == 0:             # every rank takes the same way out
+            self.sys.decomp_peer_detach()
+            raise RuntimeError(f"peer mode unavailable on at least one rank ({err})")
 
     def _detach_peers(self):
         import torch.distributed as dist

@@ -817,8 +817,15 @@ def decomp_block(gc_b200, args, rank, world, local):
     g = make()
     # the walk's bonds (0.3) span two cell edges (0.15): a three-layer position halo; halo
     # buffers sized for the beads of ~half a slab (the library reports an overflow)
-    run = decomp.DecomposedRun(g, rank, world, local, halo_layers=3,
-                               halo_capacity=max(1024, int(0.6 * beads / world)), graph_steps=10)
+    # halo through NVLink peer memory (CUDA IPC) when the box allows it, NCCL send/recv otherwise
+    kw = dict(halo_layers=3, halo_capacity=max(1024, int(0.6 * beads / world)), graph_steps=10)
+    try:
+        if os.environ.get("GC_DECOMP_PEER", "1") == "0":
+            raise RuntimeError("disabled by GC_DECOMP_PEER=0")
+        run = decomp.DecomposedRun(g, rank, world, local, peer=True, **kw)
+    except RuntimeError as ex:
+        print(f"decomp_2m: peer mode off ({ex})", file=sys.stderr)
+        run = decomp.DecomposedRun(g, rank, world, local, peer=False, **kw)
     run.begin(cfg.timestep)
     run.step(warm // 2)
     cap = run.tune_capacity()
@@ -841,6 +848,7 @@ def decomp_block(gc_b200, args, rank, world, local):
     dist.all_gather(allc, counts)
     exch = int(run.exchange_bytes_per_step)
     scheme = run.scheme
+    run.close()
     g.close()
     out = None
     if rank == 0:

@@ -141,10 +141,18 @@ if rank == 0:
         g.run(a.profile, cfg.timestep, restart=False)
         rep["single_gpu_kernels_ms"] = {k: round(v[1] / a.profile, 5) for k, v in g.profile_read().items()}
         g.profile_enable(False)
+    if a.profile and world > 1:
+        g.run(a.profile, cfg.timestep, restart=False)      # the decomposed run also took timed_phases()
     if world > 1:
         rep["speedup_vs_single_gpu"] = rep["single_gpu_ms_per_step"] / rep["decomposed_ms_per_step"]
     if a.check and x_dec is not None:
-        rep["bit_identical_to_single_gpu"] = bool(np.array_equal(g.get_positions(0), x_dec))
+        x_one = g.get_positions(0)
+        rep["bit_identical_to_single_gpu"] = bool(np.array_equal(x_one, x_dec))
+        if not rep["bit_identical_to_single_gpu"]:
+            bad = np.where(np.any(x_one != x_dec, axis=1))[0]
+            rep["mismatch"] = {"beads": int(len(bad)), "max_abs": float(np.abs(x_one - x_dec).max()),
+                               "z_min": float(x_one[bad, 2].min()), "z_max": float(x_one[bad, 2].max()),
+                               "first": bad[:8].tolist()}
     g.close()
     line = json.dumps(rep)
     print(line)
