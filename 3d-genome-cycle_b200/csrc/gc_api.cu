@@ -937,10 +937,15 @@ int check_device_errors(gc_ctx *ctx)
             return fail(ctx, GC_ERR_CAPACITY, "replica %d: contact table full (capacity %llu)", r,
                         (unsigned long long) ctx->hp.contact.capacity);
         }
-        if (st[r].error == 3) {
-            return fail(ctx, GC_ERR_STATE, "decomposed run, step %lld: a bonded partner or a moved bead lies "
-                        "outside the %d-layer halo, or a slab is thinner than the halo "
-                        "(gc_decomp_set_halo, or fewer ranks)", st[r].step, ctx->hp.dhalo);
+        if (st[r].error == 3 || (st[r].error >= 30 && st[r].error < 40)) {
+            const char *what = st[r].error == 30 ? "a bead a neighbour needs under the new grid was not in the halo "
+                                                   "shipped under the old one (peer mode)"
+                             : st[r].error == 32 ? "a bead moved past a neighbour's whole slab"
+                             : st[r].error == 33 ? "a slab is thinner than the halo"
+                             : st[r].error == 34 ? "a bonded partner is not current on the rank that needs it"
+                                                 : "halo violated";
+            return fail(ctx, GC_ERR_STATE, "decomposed run, step %lld, %d-layer halo: %s "
+                        "(gc_decomp_set_halo, or fewer ranks)", st[r].step, ctx->hp.dhalo, what);
         }
         if (st[r].error == 4) {
             return fail(ctx, GC_ERR_CAPACITY, "decomposed run, step %lld: halo buffer full (%d beads; "
@@ -2062,6 +2067,7 @@ int gc_decomp_configure(gc_ctx *ctx, int32_t rank, int32_t world)
 {
     GC_CHECK_CTX(ctx);
     if (world < 1 || rank < 0 || rank >= world) return fail(ctx, GC_ERR_INVALID, "bad rank / world");
+    if (world > GC_MAX_RANKS) return fail(ctx, GC_ERR_INVALID, "at most %d ranks", GC_MAX_RANKS);
     if (ctx->n_rep != 1) return fail(ctx, GC_ERR_STATE, "decomposition needs n_replicas = 1");
     decomp_release(ctx);
     if (world == 1) return GC_OK;

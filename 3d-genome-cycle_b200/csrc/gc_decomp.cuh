@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
     GC_PDL_ENTRY();
     RepState &st = P.st[0];
     __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2
-    if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P.drank - 1 + threadIdx.x, P.dworld, st.gdimz, P.cells_per_cut);
+    if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P, st, P.drank - 1 + threadIdx.x);
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int peer = P.dpeer;
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(256) k_decomp_pack(const __grid_constant__ Par
         if (live) x = moved[w];                     // new position, bead index in .w
         const int layer = cell_layer(st, x.z, P.cells_per_cut);
         // a bead that jumped past a neighbour's whole slab would be lost (peer mode: k_count)
-        if (!peer && live && (layer < zs[0] || layer >= zs[3])) atomicExch(&st.error, 3);
+        if (!peer && live && (layer < zs[0] || layer >= zs[3])) atomicExch(&st.error, 32);
         const bool to_lo = live && P.drank > 0 && layer < z0 + reach;
         const bool to_hi = live && P.drank + 1 < P.dworld && layer >= z1 - reach;
 #pragma unroll
@@ -168,7 +168,10 @@ __global__ void __launch_bounds__(256) k_decomp_stamp_all(const __grid_constant_
 {
     GC_PDL_ENTRY();
     const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i == 0) P.st[0].dfull = 1;
+    if (i == 0) {
+        P.st[0].dfull = 1;
+        for (int k = 0; k <= P.dworld; k++) P.st[0].dfrac[k] = (double) k / (double) P.dworld;   // equal volumes
+    }
     if (i < P.n) P.dstamp[i] = (int) P.st[0].step;
 }
 
@@ -181,8 +184,7 @@ __global__ void __launch_bounds__(256) k_decomp_owned(const __grid_constant__ Pa
     unsigned char own = 0;
     if (P.dstamp[i] == (int) st.step) {
         const int layer = cell_layer(st, P.pos[st.parity][i].z, P.cells_per_cut);
-        own = layer >= slab_start(P.drank, P.dworld, st.gdimz, P.cells_per_cut) &&
-              layer < slab_start(P.drank + 1, P.dworld, st.gdimz, P.cells_per_cut);
+        own = layer >= slab_start(P, st, P.drank) && layer < slab_start(P, st, P.drank + 1);
     }
     mask[i] = own;
 }

@@ -87,29 +87,51 @@ __device__ __forceinline__ int cell_index(const RepState &st, float4 p, int halo
     return cx + st.dims[0] * (cy + st.dims[1] * cz);
 }
 
-// First layer of rank k's slab in a grid of gdimz layers, the outer `halo` layers on either
-// side being the always-empty margin: slabs of EQUAL VOLUME of the ellipsoid the bounding box
-// encloses -- the volume fraction of an ellipsoid below height u in [-1, 1] is
-// (2 + 3u - u^3) / 4, inverted in closed form -- so that the ranks of a roughly uniformly
-// filled nucleus own similar bead counts.
-__device__ __host__ inline int slab_start(int k, int world, int gdimz, int halo)
+// First layer of a slab that starts at volume fraction f of the ellipsoid the bounding box
+// encloses, in a grid of gdimz layers whose outer `halo` layers on either side are the
+// always-empty margin.  The volume fraction of an ellipsoid below height u in [-1, 1] is
+// (2 + 3u - u^3) / 4, inverted in closed form -- so equal fractions are slabs of equal volume,
+// and the ranks of a roughly uniformly filled nucleus start out with similar bead counts.
+__device__ __host__ inline int slab_layer(double f, int gdimz, int halo)
 {
     const int nint = gdimz - 2 * halo;
-    if (k <= 0) return halo;
-    if (k >= world) return halo + nint;
-    const double f = (double) k / (double) world;
+    if (f <= 0.0) return halo;
+    if (f >= 1.0) return halo + nint;
     const double u = 2.0 * cos((acos(1.0 - 2.0 * f) + 4.0 * 3.14159265358979323846) / 3.0);
     const int z = halo + (int) floor(0.5 * (u + 1.0) * (double) nint + 0.5);
     return z < halo ? halo : (z > halo + nint ? halo + nint : z);
 }
 
+// first layer of rank k's slab in the current grid (k outside [0, world] clamps)
+__device__ __forceinline__ int slab_start(const Params &P, const RepState &st, int k)
+{
+    return st.dz[k < 0 ? 0 : (k > P.dworld ? P.dworld : k)];
+}
+
 // z-window of this rank: its slab plus the pair halo (cells_per_cut layers) on either side
 __device__ inline void decomp_window(const Params &P, RepState &st)
 {
-    const int h = P.cells_per_cut;
-    const int z0 = slab_start(P.drank, P.dworld, st.gdimz, h), z1 = slab_start(P.drank + 1, P.dworld, st.gdimz, h);
-    // a slab thinner than the position halo would need beads from beyond the neighbouring rank
-    if (z1 - z0 < P.dhalo) st.error = 3;
+    const int h = P.cells_per_cut, W = P.dworld;
+    // a slab must be at least as thick as the position halo (plus peer mode's margin): its far
+    // neighbour would otherwise need beads from beyond the near one
+    const int tmin = P.dhalo + (P.dpeer ? GC_DECOMP_PEER_MARGIN : 0);
+    int z[GC_MAX_RANKS + 1];
+    for (int k = 0; k <= W; k++) {
+        z[k] = slab_layer(k == 0 ? 0.0 : (k == W ? 1.0 : st.dfrac[k]), st.gdimz, h);
+        // an inner boundary moves by at most one layer between two plans (the halo logic,
+        // peer mode's margin in particular, relies on it); it catches up over the next steps
+        if (!st.dfull && k > 0 && k < W) z[k] = min(max(z[k], st.dz[k] - 1), st.dz[k] + 1);
+    }
+    // (slab k - 1 lies between z[k - 1] and z[k]; the two end slabs have no far neighbour and
+    // may be as thin as one layer)
+    for (int k = 1; k < W; k++) z[k] = max(z[k], z[k - 1] + (k - 1 >= 1 ? tmin : 1));
+    for (int k = W - 1; k > 0; k--) z[k] = min(z[k], z[k + 1] - (k <= W - 2 ? tmin : 1));
+    for (int k = 0; k <= W; k++) {
+        st.dz[k] = z[k];
+        const bool inner = k - 1 >= 1 && k - 1 <= W - 2;
+        if (k > 0 && z[k] - z[k - 1] < (inner ? tmin : 1)) st.error = 33;      // too many ranks for this grid
+    }
+    const int z0 = st.dz[P.drank], z1 = st.dz[P.drank + 1];
     st.zoff = z0 - h;
     st.dims[2] = (z1 - z0) + 2 * h;
     st.zown_lo = h;
@@ -285,7 +307,7 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
         const int nw = decomp_current_count(P, st);
         const int h = P.cells_per_cut;
         __shared__ int zs[4];       // slab starts of ranks drank - 1 .. drank + 2
-        if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P.drank - 1 + threadIdx.x, P.dworld, st.gdimz, h);
+        if (threadIdx.x < 4) zs[threadIdx.x] = slab_start(P, st, P.drank - 1 + threadIdx.x);
         __syncthreads();
         for (int w = i; w < nw; w += stride) {
             bool received;
@@ -307,7 +329,8 @@ __global__ void __launch_bounds__(256) k_count(const __grid_constant__ Params P)
                 const bool need_hi = P.drank + 1 < P.dworld && ln >= zs[2] - P.dhalo;
                 const bool lost = (P.drank > 1 && ln < zs[0] + P.dhalo) ||
                                   (P.drank + 2 < P.dworld && ln >= zs[3] - P.dhalo);
-                if ((need_lo && !sent_lo) || (need_hi && !sent_hi) || lost) atomicExch(&P.st[r].error, 3);
+                if ((need_lo && !sent_lo) || (need_hi && !sent_hi)) atomicExch(&P.st[r].error, 30);
+                if (lost) atomicExch(&P.st[r].error, 32);
             }
             const int c = cell_index(st, p, h);
             P.cell_of[b] = c;

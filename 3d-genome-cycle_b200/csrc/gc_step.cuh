@@ -315,7 +315,7 @@ __device__ __forceinline__ void block_reduce_commit(RepState &st, StepRed &s, bo
         q[3] = warp_sum(__double2ll_rn((double) s.w.reaction * GC_FX_SCALE));
     }
     bool bad = __any_sync(0xffffffffu, s.bad);
-    if (__any_sync(0xffffffffu, s.w.stale != 0) && lane == 0) atomicExch(&st.error, 3);
+    if (__any_sync(0xffffffffu, s.w.stale != 0) && lane == 0) atomicExch(&st.error, 34);
     __syncthreads();
     if (lane == 0) {
         for (int k = 0; k < 8; k++) sh_i[wid][k] = v[k];
@@ -585,6 +585,22 @@ __device__ inline void decomp_reduce(const Params &P, RepState &st)
     st.reaction_fx = sum[3];
     if (!err && moved != P.n) err = 4;           // a bead was lost or moved twice
     if (err) st.error = err;
+    // Load balance: nudge every slab boundary towards equal bead counts (the equal-volume cut
+    // assumes a uniformly filled ellipsoid).  Integral control on the cumulative counts, a
+    // tenth of the error per step -- far less than a layer, so a boundary moves by at most one
+    // layer between two plans, which the halo logic relies on.  Same inputs on every rank.
+    if (!err) {
+        long long below = 0;
+        for (int k = 1; k < P.dworld; k++) {
+            const int *hi = reinterpret_cast<const int *>(P.dhdr_all + (size_t) (k - 1) * DHDR + 4);
+            below += hi[7];
+            const double want = (double) k / (double) P.dworld;
+            double f = st.dfrac[k] + 0.1 * (want - (double) below / (double) P.n);
+            const double lo = st.dfrac[k - 1] + 1.0e-4;
+            f = f < lo ? lo : f;
+            st.dfrac[k] = f > 1.0 - 1.0e-4 ? 1.0 - 1.0e-4 : f;
+        }
+    }
 }
 
 // after k_finish<STEP_FUSED> (fixed dt) or k_integrate (adaptive dt)

@@ -136,6 +136,8 @@ struct StepConst {
 
 // Per-replica mutable scalars.  Written only by the last block of a step (or
 // by the host between runs); read by every block at kernel start.
+constexpr int GC_MAX_RANKS = 16;          // ranks of a decomposed run
+
 struct RepState {
     // --- context (double, as the reference's interphase_context) ---
     double time;
@@ -172,6 +174,11 @@ struct RepState {
     // z-window of a decomposed run: dims[2] counts the LOCAL layers [zoff, zoff + dims[2]) of the
     // global grid (gdimz layers); the local layers [zown_lo, zown_hi) are owned by this rank
     int zoff, gdimz, zown_lo, zown_hi;
+    // slab boundaries of all ranks: dfrac[k] = volume fraction of the bounding ellipsoid below
+    // rank k's slab (k / world at restart, then nudged every step towards equal bead counts,
+    // identically on every rank: decomp_reduce), dz[k] = its first layer in the current grid
+    double dfrac[GC_MAX_RANKS + 1];
+    int dz[GC_MAX_RANKS + 1];
     // the beads current on this rank, as a work list for the next cell-list build: the sorted
     // slots [dprev_lo, dprev_hi) it moved in the last step (bead index in spos[].w) plus the
     // two received halo buffers; dfull = 1: all N beads (after gc_run(restart = 1))

@@ -139,7 +139,10 @@ def test_decomposed_200k_polymer_is_bit_identical_and_exchanges_a_surface(world,
     sent = [lo + hi for lo, hi in ex.halo_counts()]
     # equal-volume slabs: balanced ownership; the halo is a surface term -- a small fraction
     # of a thick slab (2 ranks: ~25 layers each), most of a thin one (8 ranks: ~6 layers)
-    assert max(owned) < 1.25 * n / world, owned
+    # (8 ranks: a layer is a sixth of a slab here, and inner slabs keep a minimum thickness)
+    assert max(owned) < (1.25 if world < 8 else 1.5) * n / world, owned
+    if world == 8:
+        print("owned per rank after", steps, "steps:", owned)
     if world == 2:
         assert max(sent) < 0.3 * max(owned), (sent, owned)
     for g in ranks:
@@ -154,8 +157,8 @@ def test_decomposed_context_rejects_plain_run_and_reports_a_thin_halo():
     with pytest.raises(gc_b200.api.GcError):
         g.run(5, cfg.timestep)
     g.close()
-    # 40 ranks over a grid of a few dozen layers: slabs thinner than the halo
-    ranks = [_interphase_rank(d, cfg, x) for _ in range(40)]
+    # 16 ranks over a grid of about ten layers: inner slabs thinner than the halo
+    ranks = [_interphase_rank(d, cfg, x) for _ in range(16)]
     ex = decomp.LocalExchange(ranks)
     with pytest.raises(gc_b200.api.GcError, match="halo"):
         ex.begin(cfg.timestep)
