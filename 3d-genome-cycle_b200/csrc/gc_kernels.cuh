@@ -518,7 +518,8 @@ __device__ __forceinline__ void gather_slot(const Params &P, RepState &st, int r
     {
         // pair-interleaved copy (k_pair_cells stages whole units), paired per layer
         const int dxy = st.dims[0] * st.dims[1];
-        const int L = c / dxy;
+        // (= c / dxy without the integer division: the layer cell_index used)
+        const int L = cell_layer(st, p.z, P.cells_per_cut) - st.zoff;
         const int lstart = start[L * dxy], lend = start[(L + 1) * dxy];
         const int us = unit_slot(dst, L, lstart);
         float *u0 = unit_half(P, r, us, 0), *u1 = unit_half(P, r, us, 1);

@@ -64,8 +64,8 @@ CTX_FIELDS = ("time", "semiaxes", "core_scale", "bond_scale", "contact_distance"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)      # 20 x 500 = the whole 10^4-step window
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--replicas", type=int, default=8, help="cell trajectories per GPU")
     ap.add_argument("--sim-steps", type=int, default=500, help="simulation steps per bench step")
