@@ -186,34 +186,26 @@ constexpr int TICKET = GC_TICKET;       // cells per work-queue claim (1 or 2)
 static_assert(TICKET == 1 || TICKET == 2, "cells per claim");
 constexpr int CH2MAX = 16 * HB;          // home beads per staged tile (16 lanes x HB)
 
-template<bool PLAIN, int MINB>
-__global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
-                                                        int use_enabled)
+// read-only path for the launch-per-step kernels; plain loads when the arrays are rewritten
+// inside the same kernel (the persistent small-system kernel, where they live in shared memory)
+template<bool NC, typename T>
+__device__ __forceinline__ T pair_ld(const T *p)
 {
-    GC_PDL_ENTRY();
-    __shared__ __align__(16) PairUnit s_tile[CW][TILE_UNITS];
+    if (NC) return __ldg(p);
+    return *p;
+}
 
-    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
-
-    if (!pair_on) {                                            // block-uniform
-        const size_t total = (size_t) P.n_rep * P.n;
-        for (size_t t = (size_t) blockIdx.x * (CW * 32) + threadIdx.x; t < total;
-             t += (size_t) gridDim.x * (CW * 32)) {
-            P.pforce[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        return;
-    }
-
-    PairUnit *tile = s_tile[warp];
+// All home cells of replica r that this warp gets hold of: from the shared work queue
+// (PERSIST = false: atomic claims, any number of blocks) or a static share of it
+// (PERSIST = true: warp `slot` of `nslots`, one block per replica).  The arithmetic per home
+// cell -- staging order, culling, lane split, fold -- is the same either way.
+template<bool PLAIN, bool PERSIST>
+__device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st, int r, PairUnit *tile, int lane,
+                                                   int slot, int nslots)
+{
     const unsigned lt_mask = (1u << lane) - 1u;
-
-    // Blocks are not tied to a replica: every warp works through the queues of all
-    // replicas round-robin, starting at a different one.
-    for (int rr = 0; rr < P.n_rep; rr++) {
-    const int r = (blockIdx.x + rr) % P.n_rep;
-    RepState &st = P.st[r];
+    int next_cell = slot * TICKET;
+    (void) next_cell;
     const StepConst &sc = st.sc;
     const size_t ro = (size_t) r * P.n;
     const float4 *__restrict__ sp = P.spos[st.parity] + ro;
@@ -240,26 +232,32 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
         // descriptor -> row starts (three L2 round trips) is paid once per claim, and the
         // loads of the second cell are in flight while the first is evaluated.
         int kk0 = 0;
-        if (lane == 0) kk0 = atomicAdd(&st.cell_cursor, TICKET);
-        kk0 = __shfl_sync(0xffffffffu, kk0, 0);
+        if (PERSIST) {
+            // one block owns the replica: warp `slot` of `nslots` takes cells slot, slot + nslots, ...
+            kk0 = next_cell;
+            next_cell += nslots * TICKET;
+        } else {
+            if (lane == 0) kk0 = atomicAdd(&st.cell_cursor, TICKET);
+            kk0 = __shfl_sync(0xffffffffu, kk0, 0);
+        }
         if (kk0 >= nused) break;
         // (scalars, not arrays: the second cell's five values stay in registers)
         const int kA_ = kk0, kB_ = min(kk0 + 1, nused - 1);
-        const int4 cellA = __ldg(&cells[kA_ < nheavy ? kA_ : P.n - 1 - (kA_ - nheavy)]);
+        const int4 cellA = pair_ld<!PERSIST>(&cells[kA_ < nheavy ? kA_ : P.n - 1 - (kA_ - nheavy)]);
         int4 cellB = cellA;
-        if (TICKET == 2) cellB = __ldg(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
+        if (TICKET == 2) cellB = pair_ld<!PERSIST>(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
         int loA = 0, u1A = 0, loB = 0, u1B = 0;
         if (lane < 9) {
             // slots -> the layer-relative unit space of the pair-interleaved copy (unit_slot)
             const int LA = cellA.w + lane / 3 - 1;
-            const int sA = unit_slot(0, LA, __ldg(&start[LA * dxy]));
-            loA = __ldg(&start[cellA.x + row_rel]) + sA;
-            u1A = (__ldg(&start[cellA.x + row_rel + 3]) + sA + 1) >> 1;
+            const int sA = unit_slot(0, LA, pair_ld<!PERSIST>(&start[LA * dxy]));
+            loA = pair_ld<!PERSIST>(&start[cellA.x + row_rel]) + sA;
+            u1A = (pair_ld<!PERSIST>(&start[cellA.x + row_rel + 3]) + sA + 1) >> 1;
             if (TICKET == 2) {
                 const int LB = cellB.w + lane / 3 - 1;
-                const int sB = unit_slot(0, LB, __ldg(&start[LB * dxy]));
-                loB = __ldg(&start[cellB.x + row_rel]) + sB;
-                u1B = (__ldg(&start[cellB.x + row_rel + 3]) + sB + 1) >> 1;
+                const int sB = unit_slot(0, LB, pair_ld<!PERSIST>(&start[LB * dxy]));
+                loB = pair_ld<!PERSIST>(&start[cellB.x + row_rel]) + sB;
+                u1B = (pair_ld<!PERSIST>(&start[cellB.x + row_rel + 3]) + sB + 1) >> 1;
             }
         }
         int h0 = cellA.y, nhome = cellA.z, lo = loA, u1 = u1A;
@@ -299,7 +297,7 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
             // the shifted coordinates order like the floats: one REDUX per bound.
             float2 blx, bly, blz, bhx, bhy, bhz;
             {
-                const float4 hp = __ldg(&sp[h0 + g0 + min(lane, ng - 1)]);
+                const float4 hp = pair_ld<!PERSIST>(&sp[h0 + g0 + min(lane, ng - 1)]);
                 const unsigned ux = __float_as_uint(hp.x - ox), uy = __float_as_uint(hp.y - oy);
                 const unsigned uz = __float_as_uint(hp.z - oz);
                 float v;
@@ -327,10 +325,10 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
                     row += k >= t ? step : 0;
                 }
                 const int u = k + __shfl_sync(0xffffffffu, shift, row);
-                const float4 a = __ldg(&uxy[u]);
-                float4 b = __ldg(&uzA[u]);
+                const float4 a = pair_ld<!PERSIST>(&uxy[u]);
+                float4 b = pair_ld<!PERSIST>(&uzA[u]);
                 float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (!PLAIN) bb = __ldg(&uB[u]);
+                if (!PLAIN) bb = pair_ld<!PERSIST>(&uB[u]);
                 // distance of both beads of the unit from the box (packed)
                 const float2 x2 = make_float2(a.x, a.y), y2 = make_float2(a.z, a.w), z2 = make_float2(b.x, b.y);
                 const float2 lx = __fadd2_rn(blx, make_float2(-x2.x, -x2.y)), hx = __fadd2_rn(x2, bhx);
@@ -368,11 +366,11 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
 #pragma unroll
                         for (int j = 0; j < HB; j++) {
                             const int t = h0 + g0 + min(HB * hl + j, ng - 1);
-                            const float4 me = __ldg(&sp[t]);
+                            const float4 me = pair_ld<!PERSIST>(&sp[t]);
                             hm.nx[j] = -me.x; hm.ny[j] = -me.y; hm.nz[j] = -me.z;
                             hm.A[j] = hA; hm.B[j] = 0.0f;
                             if (!PLAIN) {
-                                const float2 abi = __ldg(&sab[t]);
+                                const float2 abi = pair_ld<!PERSIST>(&sab[t]);
                                 hm.A[j] = hA * abi.x; hm.B[j] = hB * abi.y;
                             }
                         }
@@ -393,7 +391,34 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
         }
         }   // cells of this claim
     }
-    }   // replicas
+}
+
+template<bool PLAIN, int MINB>
+__global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_constant__ Params P, unsigned mask_arg,
+                                                        int use_enabled)
+{
+    GC_PDL_ENTRY();
+    __shared__ __align__(16) PairUnit s_tile[CW][TILE_UNITS];
+
+    const unsigned mask = use_enabled ? P.enabled : (mask_arg & P.enabled);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool pair_on = P.pair.mode != PAIR_NONE && (mask >> P.pair.term & 1u);
+
+    if (!pair_on) {                                            // block-uniform
+        const size_t total = (size_t) P.n_rep * P.n;
+        for (size_t t = (size_t) blockIdx.x * (CW * 32) + threadIdx.x; t < total;
+             t += (size_t) gridDim.x * (CW * 32)) {
+            P.pforce[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+
+    // Blocks are not tied to a replica: every warp works through the queues of all
+    // replicas round-robin, starting at a different one.
+    for (int rr = 0; rr < P.n_rep; rr++) {
+        const int r = (blockIdx.x + rr) % P.n_rep;
+        pair_cells_replica<PLAIN, false>(P, P.st[r], r, s_tile[warp], lane, 0, 1);
+    }
 }
 
 } // namespace gc
