@@ -24,7 +24,6 @@
 #include "gc_cells.cuh"
 #include "gc_contact.cuh"
 #include "gc_decomp.cuh"
-#include "gc_persist.cuh"
 #include "gc_transition.cuh"
 #include "gc_peak.cuh"
 
@@ -58,7 +57,6 @@ struct gc_ctx {
     // device allocations (freed in gc_destroy)
     std::vector<void *> allocs;
     std::vector<void *> ipc_mapped;          // peer buffers opened with cudaIpcOpenMemHandle
-    int persist_smem_max = -1;               // dynamic shared memory k_persist_small may use (-1: not asked yet)
     float *d_mob = nullptr;
     float2 *d_ab = nullptr;
     int *d_flags = nullptr, *d_bond_off = nullptr, *d_triple_off = nullptr, *d_tether_off = nullptr;
@@ -923,59 +921,6 @@ void launch_rebuild(gc_ctx *ctx)
     LAUNCH(ctx, k_gather, g, 256, ctx->hp);
 }
 
-int check_device_errors(gc_ctx *ctx);
-
-// The persistent small-system kernel: true if it took the whole run.
-bool persist_launch(gc_ctx *ctx, const gc_run_config *c, bool adaptive)
-{
-    const Params &P = ctx->hp;
-    const bool off = getenv("GC_NO_PERSIST") != nullptr;     // (read per call: the parity test flips it)
-    if (off || !small_path(ctx) || adaptive || c->noise || P.contact.enabled || P.skin > 0.0f ||
-        P.wall.term >= 0 || c->steps < 8 || ctx->profiling) {
-        return false;
-    }
-    constexpr auto k_plain = k_persist_small<true>;
-    constexpr auto k_ab = k_persist_small<false>;
-    const bool plain = P.pair.mode != PAIR_AB;
-    if (ctx->persist_smem_max < 0) {
-        ctx->persist_smem_max = 0;
-        cudaFuncAttributes fa{};
-        int optin = 0;
-        if (cudaFuncGetAttributes(&fa, plain ? (const void *) k_plain : (const void *) k_ab) == cudaSuccess &&
-            cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device) == cudaSuccess) {
-            const int room = optin - (int) fa.sharedSizeBytes;
-            if (room > 0 &&
-                cudaFuncSetAttribute(k_plain, cudaFuncAttributeMaxDynamicSharedMemorySize, room) == cudaSuccess &&
-                cudaFuncSetAttribute(k_ab, cudaFuncAttributeMaxDynamicSharedMemorySize, room) == cudaSuccess) {
-                ctx->persist_smem_max = room;
-            }
-        }
-        cudaGetLastError();
-    }
-    const PersistLayout L = persist_layout(ctx->n, P.n_units, -1, (unsigned) ctx->persist_smem_max);
-    if (L.pair_warps < 4 || (int) L.total > ctx->persist_smem_max) return false;     // does not fit: three kernels per step
-
-    prof_begin(ctx, "k_persist_small");
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(ctx->n_rep);
-    cfg.blockDim = dim3(SMALL_BS);
-    cfg.dynamicSmemBytes = L.total;
-    cfg.stream = ctx->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = ctx->pdl ? 1 : 0;
-    if (plain) cudaLaunchKernelEx(&cfg, k_plain, ctx->hp, (long long) c->steps, L.pair_warps);
-    else cudaLaunchKernelEx(&cfg, k_ab, ctx->hp, (long long) c->steps, L.pair_warps);
-    prof_end(ctx);
-    ctx->launches++;
-    ctx->run_step += c->steps;
-    if (c->steps & 1) ctx->parity ^= 1;
-    launch_rebuild(ctx);              // the global sorted copies follow the positions written back
-    return true;
-}
-
 int check_device_errors(gc_ctx *ctx)
 {
     GC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1266,9 +1211,6 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
 
     const long long interval = P.contact.enabled ? P.contact.interval : 0;
     const dim3 g = bead_grid(ctx, BS);
-    // small systems, fixed dt, nothing but forces and the update: all steps in ONE launch of
-    // the persistent kernel (gc_persist.cuh), then the global cell list is rebuilt once
-    if (persist_launch(ctx, c, adaptive)) return check_device_errors(ctx);
     const bool graphable = !adaptive && !c->noise && c->steps >= 64 && ensure_step_graph(ctx, interval);
     const int B = graphable ? ctx->step_graph_steps : 0;
     // small path, fixed dt: every step's epilogue leaves the cell list of the next step

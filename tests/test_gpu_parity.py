@@ -724,52 +724,3 @@ def test_set_step_resumes_a_run_bit_for_bit():
     np.testing.assert_array_equal(h.get_positions_f32(0), xb)
     assert h.get_context(0).step == 160
 
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("stage", ["anatelophase", "prometaphase"])
-def test_persistent_small_system_kernel_is_bit_identical(stage, monkeypatch):
-    """The mitotic stages run all steps of a gc_run call in ONE launch of k_persist_small (a
-    block per replica, state in shared memory).  It calls the same device functions as the
-    three-kernels-per-step path, so positions and context must agree bit for bit
-    (GC_NO_PERSIST=1 selects the latter), also across chunked calls and for several replicas."""
-    import dataclasses
-    d, _, _ = small_interphase(scale=0.3, radius=1.0)
-    mcfg = synth.MitoticConfig()
-    sisters = stage == "prometaphase"
-    if sisters:
-        mcfg = dataclasses.replace(mcfg, polar_ejection_force=0.8, polar_ejection_cross_section=0.25)
-    md = synth.make_mitotic_design(d, mcfg, sisters=sisters)
-    x = synth.quantize_f32(synth.rod_positions(md, mcfg, seed=3)).astype(np.float64)
-    R = 3
-
-    def run(persist):
-        if persist:
-            monkeypatch.delenv("GC_NO_PERSIST", raising=False)
-        else:
-            monkeypatch.setenv("GC_NO_PERSIST", "1")
-        g = gc_b200.System(md.n, R, 0)
-        if sisters:
-            stages.setup_prometaphase(g, md, mcfg)
-        else:
-            t = stages.setup_anatelophase(g, md, mcfg)
-            stages.enter_anaphase(g, t)
-        g.set_positions(x)
-        g.set_seeds([5, 6, 7])
-        l0 = g.launch_count()
-        g.run(230, mcfg.timestep)
-        g.run(71, mcfg.timestep, restart=False)
-        if not sisters:
-            stages.enter_telophase(g, t)
-            g.run(100, mcfg.timestep, restart=False)
-        launches = g.launch_count() - l0
-        out = [g.get_positions(r) for r in range(R)], [g.get_context(r).time for r in range(R)], g.compute_energy()
-        g.close()
-        return out, launches
-
-    (xp, tp, ep), lp = run(True)
-    (xs, ts, es), ls = run(False)
-    assert lp < ls / 20, (lp, ls)                 # it did take the persistent path
-    for a, b in zip(xp, xs):
-        np.testing.assert_array_equal(a, b)
-    assert tp == ts and ep == es
-    assert np.abs(xp[0] - xp[1]).max() > 1e-3     # replicas differ (seeds)
