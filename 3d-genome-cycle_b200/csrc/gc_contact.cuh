@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_contact_cells(co
     const int nheavy = st.n_used_cells, nused = nheavy + st.n_light_cells;
     const int dx = st.dims[0], dxy = st.dims[0] * st.dims[1];
     const int row_rel = lane < nrows ? (lane % side - M) * dx + (lane / side - M) * dxy - M : 0;
+    const float ox = st.origin[0], oy = st.origin[1], oz = st.origin[2];
     int head = 0, qn = 0;
 
     // one lane per queued hit: exact predicate, then the table insert
@@ -97,24 +98,62 @@ __global__ void __launch_bounds__(CW * 32, GC_CELL_MINBLOCKS) k_contact_cells(co
         if (lane == 0) sm.row_off[32] = total;
         __syncwarp();
 
+        // Bounding box of the cell's home beads: a candidate further than the contact distance
+        // from the box is further than that from every home bead.  x - origin > 0 for every
+        // bead (the origin lies a cell below the bounding box), so the raw bits of the shifted
+        // coordinates order like the floats: one REDUX per bound.
+        float blo[3], bhi[3];
+        {
+            unsigned ulo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, uhi[3] = {0u, 0u, 0u};
+            for (int g0 = 0; g0 < nhome; g0 += 32) {
+                const float4 hp = __ldg(&sp[h0 + min(g0 + lane, nhome - 1)]);
+                const unsigned u[3] = {__float_as_uint(hp.x - ox), __float_as_uint(hp.y - oy),
+                                       __float_as_uint(hp.z - oz)};
+                for (int k = 0; k < 3; k++) {
+                    ulo[k] = min(ulo[k], __reduce_min_sync(0xffffffffu, u[k]));
+                    uhi[k] = max(uhi[k], __reduce_max_sync(0xffffffffu, u[k]));
+                }
+            }
+            blo[0] = __uint_as_float(ulo[0]) + ox; bhi[0] = __uint_as_float(uhi[0]) + ox;
+            blo[1] = __uint_as_float(ulo[1]) + oy; bhi[1] = __uint_as_float(uhi[1]) + oy;
+            blo[2] = __uint_as_float(ulo[2]) + oz; bhi[2] = __uint_as_float(uhi[2]) + oz;
+        }
+
         for (int c0 = 0; c0 < total; c0 += CCAP) {             // tile chunks (usually one)
-            const int nt = min(CCAP, total - c0);
+            const int nin = min(CCAP, total - c0);
+            int nt = 0;                                        // candidates kept in the tile
             if (c0 > 0) __syncwarp();
             {
                 int row = 0, end = sm.row_off[1], shift = sm.row_shift[0];
-                for (int k = c0 + lane; k < c0 + nt; k += 32) {
-                    if (k >= end) {
-                        do {
-                            row++;
-                            end = sm.row_off[row + 1];
-                        } while (k >= end);
-                        shift = sm.row_shift[row];
+                for (int kk = c0; kk < c0 + nin; kk += 32) {
+                    const int k = kk + lane;
+                    bool keep = false;
+                    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (k < c0 + nin) {
+                        if (k >= end) {
+                            do {
+                                row++;
+                                end = sm.row_off[row + 1];
+                            } while (k >= end);
+                            shift = sm.row_shift[row];
+                        }
+                        q = __ldg(&sp[k + shift]);
+                        const float ex = fmaxf(fmaxf(blo[0] - q.x, q.x - bhi[0]), 0.0f);
+                        const float ey = fmaxf(fmaxf(blo[1] - q.y, q.y - bhi[1]), 0.0f);
+                        const float ez = fmaxf(fmaxf(blo[2] - q.z, q.z - bhi[2]), 0.0f);
+                        // (a hair of slack on top of the band limit: the box bounds were
+                        //  rebuilt from shifted coordinates)
+                        keep = fmaf(ex, ex, fmaf(ey, ey, ez * ez)) <= lim * 1.0002f;
                     }
-                    const float4 q = __ldg(&sp[k + shift]);
-                    tx[k - c0] = q.x;
-                    ty[k - c0] = q.y;
-                    tz[k - c0] = q.z;
-                    tj[k - c0] = __float_as_int(q.w);
+                    const unsigned m = __ballot_sync(0xffffffffu, keep);
+                    if (keep) {
+                        const int t = nt + __popc(m & lt_mask);
+                        tx[t] = q.x;
+                        ty[t] = q.y;
+                        tz[t] = q.z;
+                        tj[t] = __float_as_int(q.w);
+                    }
+                    nt += __popc(m);
                 }
             }
             __syncwarp();
