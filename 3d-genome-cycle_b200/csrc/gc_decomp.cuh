@@ -9,22 +9,26 @@
 // carries the step at which this rank last wrote it (Params::dstamp); a bead that left
 // the halo simply stops being current and drops out of the cell list.
 //
-// One step on rank k:
-//   gc_decomp_step_compute   cell list over the window [z0 - 1, z1 + 1), pair forces of the
-//                            owned layers, k_finish moves the owned beads (new position in
-//                            pos[], stamp = step + 1), k_decomp_header writes the rank's
-//                            share of the per-step reductions (bounding box, wall sums,
-//                            error) to a 128-byte header
+// One step on rank k (send / receive scheme):
+//   gc_decomp_step_compute   cell list over the window [z0 - 1, z1 + 1) built from the work
+//                            list of current beads (k_count takes the halo copies received
+//                            after the previous step in on its way), pair forces of the owned
+//                            layers, k_finish moves the owned beads (new position in pos[] and,
+//                            in slot order, spos[]; stamp = step + 1), k_decomp_header writes
+//                            the rank's share of the per-step reductions (bounding box, wall
+//                            sums, error, bead count) to a 128-byte header
 //   all-gather of the headers (world x 128 bytes; NCCL)
-//   gc_decomp_step_pack      k_finalize_step folds the headers (decomp_reduce), its per-step
-//                            callback body plans the NEXT grid (identical on every rank);
-//                            k_decomp_pack appends each moved bead whose new layer lies
-//                            within dhalo layers of the neighbour's new slab -- or inside
-//                            it: ownership follows the position -- to the send buffer of
-//                            that neighbour, as (x, y, z, bead)
+//   gc_decomp_step_pack      k_finalize_step folds the headers (decomp_reduce: reductions,
+//                            load balance), its per-step callback body plans the NEXT grid
+//                            (identical on every rank); k_decomp_pack appends each moved bead
+//                            whose new layer lies within dhalo layers of the neighbour's new
+//                            slab -- or inside it: ownership follows the position -- to the
+//                            send buffer of that neighbour, as (x, y, z, bead)
 //   send/recv with rank - 1 and rank + 1 (NCCL point-to-point over NVLink)
-//   gc_decomp_step_commit    k_decomp_unpack writes the received beads by bead index and
-//                            stamps them current
+// Peer mode (gc_decomp_peer_*): k_decomp_pack runs inside gc_decomp_step_compute, under the
+// grid of the step just taken plus GC_DECOMP_PEER_MARGIN layers, and stores straight into the
+// neighbours' double-buffered receive buffers over NVLink; the header all-gather is then the
+// step's only collective, and the next k_count verifies the shipped set against the new grid.
 //
 // The exchange is O(surface): 2 neighbours x (beads in dhalo + 1 layers) x 16 bytes instead
 // of round 1's all-gather of all N beads to every rank.  Every bead's force is still a

@@ -13,8 +13,11 @@ namespace gc {
 
 // Single-bead terms + update (or force output), one thread per sorted slot, full
 // occupancy; consumes the nonbonded force of k_pair_cells.
+#ifndef GC_FINISH_MINB
+#define GC_FINISH_MINB 1
+#endif
 template<int MODE>
-__global__ void __launch_bounds__(BS) k_finish(const __grid_constant__ Params P, unsigned mask_arg, int use_enabled)
+__global__ void __launch_bounds__(BS, GC_FINISH_MINB) k_finish(const __grid_constant__ Params P, unsigned mask_arg, int use_enabled)
 {
     GC_PDL_ENTRY();
     const int r = blockIdx.y;
