@@ -724,3 +724,64 @@ def test_set_step_resumes_a_run_bit_for_bit():
     np.testing.assert_array_equal(h.get_positions_f32(0), xb)
     assert h.get_context(0).step == 160
 
+
+
+# ---------------------------------------------------------------------------
+# edge cases (shapes of MDT/forcefield/test_neighbor_pairwise_forcefield.cc:37-94 and
+# MDT/forcefield/test_bonded_*: empty and tiny systems, ragged chains, crowded cells)
+# ---------------------------------------------------------------------------
+def _plain_system(make, n, chains, x, eps=2.0, sigma=0.3):
+    s = make(n)
+    s.set_bead_attrs(np.full(n, 0.1))
+    s.add_pair_softcore(eps, sigma)
+    bonds = stages.chain_bonds(chains)
+    if len(bonds):
+        s.add_bonds(bonds, gc_b200.api.GC_BOND_SEMISPRING, K_a=1000.0, l_a=0.3)
+    tri = stages.chain_triples(chains)
+    if len(tri):
+        s.add_triples(tri, 1.0)
+    s.set_positions(x)
+    return s
+
+
+@pytest.mark.parametrize("case", ["one_bead", "two_coincident", "line_at_cutoff", "ragged_chains",
+                                  "crowded_cell"])
+def test_edge_case_forces_and_steps(oracle_kind, case):
+    rng = np.random.default_rng(11)
+    f32 = lambda a: np.asarray(a, dtype=np.float32).astype(np.float64)
+    if case == "one_bead":                       # no pair, no bond: zero force, pure diffusion
+        n, chains, x = 1, [(0, 1)], f32([[0.1, -0.2, 0.3]])
+    elif case == "two_coincident":               # r = 0: the soft core's force factor is finite, F = 0
+        n, chains, x = 2, [(0, 1), (1, 2)], f32([[0.5, 0.5, 0.5], [0.5, 0.5, 0.5]])
+    elif case == "line_at_cutoff":               # neighbours exactly at sigma and one ulp either side
+        s = np.float32(0.3)
+        xs = np.cumsum([0.0, s, np.nextafter(s, np.float32(1)), np.nextafter(s, np.float32(0)), 0.5 * s])
+        n, chains, x = 5, [(0, 5)], f32(np.stack([xs, np.zeros(5), np.zeros(5)], axis=1))
+    elif case == "ragged_chains":                # chains of 1, 2, 3 and 40 beads: bonds / triples per length
+        chains = [(0, 1), (1, 3), (3, 6), (6, 46)]
+        n = 46
+        x = f32(rng.normal(size=(n, 3)) * 0.4)
+    else:                                        # 700 beads inside ONE cell: 44 home groups, tile overflow passes
+        n, chains = 700, [(0, 700)]
+        x = f32(rng.random((n, 3)) * 0.28)
+    g, o = _plain_system(gpu, n, chains, x), _plain_system(oracle(oracle_kind), n, chains, x)
+    Fg, Fo = g.compute_force(), o.compute_force()
+    assert np.all(np.isfinite(Fg))
+    if np.abs(Fo).max() > 0:
+        assert rel_force_err(Fg, Fo) <= 1e-5
+    else:
+        assert np.abs(Fg).max() == 0.0
+    assert g.compute_energy() == pytest.approx(o.compute_energy(), rel=2e-5, abs=1e-9)
+    if case == "two_coincident":
+        assert np.abs(Fg).max() == 0.0
+    # a few fused steps under identical injected noise (zero steps first: a no-op)
+    x0 = g.get_positions()
+    g.run(0, 1e-5)
+    np.testing.assert_array_equal(g.get_positions(), x0)
+    steps = 8
+    noise = rng.normal(size=(1, steps, n, 3))
+    g.run(steps, 1e-5, noise=noise)
+    o.run(steps, 1e-5, noise=noise)
+    scale = max(1.0, np.abs(o.get_positions()).max())
+    assert np.abs(g.get_positions() - o.get_positions()).max() <= 1e-5 * scale
+    g.close()
