@@ -41,6 +41,7 @@ import json
 import os
 import subprocess
 import sys
+import threading
 import tempfile
 import time
 from pathlib import Path
@@ -80,6 +81,8 @@ def parse_args():
     ap.add_argument("--no-r1", action="store_true")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the force_100k (N = 1) / decomp_2m (N > 1) blocks")
+    ap.add_argument("--extra-timeout", type=float, default=240.0,
+                    help="seconds the decomp_2m block may take before the line is emitted without it")
     ap.add_argument("--profile-steps", type=int, default=60)
     ap.add_argument("--decomp-beads", type=int, default=2_000_000)
     # internal: one pinned CPU worker of the reference legs
@@ -709,6 +712,18 @@ def run_b200_arm(args):
             "fp32_frac": (FLOP_PER_PAIR * p_mean + FLOP_SINGLE_BEAD) * value / world / 1e12 / fp32_peak,
             "hbm_frac": ALG_BYTES_PER_BEAD_STEP * value / world / 1e9 / hbm_peak}
 
+    def headline():
+        return {
+            "metric": "bead-steps/s", "value": value, "unit": "bead-steps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(design, args, how, window),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roof, "cpu_baseline": None, "r1": r1,
+            "window_end": {"step": int(ctx_end.step), "semiaxis_x": float(ctx_end.semiaxes[0]),
+                           "core_scale": float(ctx_end.core_scale)},
+        }
+
     # ---- configs[3] on one GPU / configs[4] over the GPUs of this run -------------------
     extra = {}
     if not args.no_extra and args.scale == 1.0:
@@ -717,9 +732,32 @@ def run_b200_arm(args):
         del flush_buf
         torch.cuda.empty_cache()
         if world == 1:
-            extra["force_100k"] = force_100k_block(gc_b200, local)
+            try:
+                extra["force_100k"] = force_100k_block(gc_b200, local)
+            except Exception as ex:                       # the headline numbers must still get out
+                extra["force_100k"] = {"error": repr(ex)[:300]}
         else:
-            extra["decomp_2m"] = decomp_block(gc_b200, args, rank, world, local)
+            # The decomposed polymer is a second, collective workload behind the ensemble timing:
+            # a rank that fails or stalls in it must not take the line above with it.  A watchdog
+            # thread emits the line without the block and ends the process when it takes too long.
+            def bail(why):
+                if rank == 0:
+                    line = headline()
+                    line["decomp_2m"] = {"error": why}
+                    emit(line)
+                sys.stderr.flush()
+                os._exit(0)
+
+            wd = threading.Timer(args.extra_timeout, bail, args=(f"no result after {args.extra_timeout} s",))
+            wd.daemon = True
+            wd.start()
+            try:
+                extra["decomp_2m"] = decomp_block(gc_b200, args, rank, world, local)
+            except Exception as ex:
+                wd.cancel()
+                print(f"decomp_2m failed on rank {rank}: {ex!r}", file=sys.stderr)
+                bail(repr(ex)[:300])                      # the other ranks leave through their watchdogs
+            wd.cancel()
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) --------------------------
     cpu = None
@@ -741,16 +779,8 @@ def run_b200_arm(args):
         pool.close()
 
     if rank == 0:
-        line = {
-            "metric": "bead-steps/s", "value": value, "unit": "bead-steps/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(design, args, how, window),
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": roof, "cpu_baseline": cpu, "r1": r1,
-            "window_end": {"step": int(ctx_end.step), "semiaxis_x": float(ctx_end.semiaxes[0]),
-                           "core_scale": float(ctx_end.core_scale)},
-        }
+        line = headline()
+        line["cpu_baseline"] = cpu
         line.update(extra)
         emit(line)
     if g is not None:
