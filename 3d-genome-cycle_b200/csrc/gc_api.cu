@@ -57,6 +57,7 @@ struct gc_ctx {
     // device allocations (freed in gc_destroy)
     std::vector<void *> allocs;
     std::vector<void *> ipc_mapped;          // peer buffers opened with cudaIpcOpenMemHandle
+    bool decomp_all_current = false;         // every bead was stamped current and no step has run since
     float *d_mob = nullptr;
     float2 *d_ab = nullptr;
     int *d_flags = nullptr, *d_bond_off = nullptr, *d_triple_off = nullptr, *d_tether_off = nullptr;
@@ -702,6 +703,12 @@ int gc_set_step(gc_ctx *ctx, int32_t replica, int64_t step)
     });
     if (rc) return rc;
     ctx->run_step = step;      // host mirror (contact cadence, graph alignment): replicas move in lockstep
+    // a decomposed context marks "current on this rank" with the step number: resuming at
+    // another step (after gc_set_positions with all N beads) re-stamps them all
+    if (ctx->hp.decomp) {
+        k_decomp_stamp_all<<<(ctx->n + 255) / 256, 256, 0, ctx->stream>>>(ctx->hp);
+        ctx->decomp_all_current = true;
+    }
     return GC_OK;
 }
 
@@ -1204,8 +1211,11 @@ int gc_run(gc_ctx *ctx, const gc_run_config *c)
         // restart: every rank holds all N positions (gc_set_positions), all are current.
         // Otherwise only the parameters were refreshed: the grid of the last step stands,
         // and a bounding box over this rank's partly stale positions would be wrong.
-        if (!c->restart) return GC_OK;
-        LAUNCH(ctx, k_decomp_stamp_all, (ctx->n + 255) / 256, 256, ctx->hp);
+        // (unless every bead is still current: right after a restart or gc_set_step, where a
+        //  changed context -- core_scale sets the cell edge -- must reach the plan)
+        if (!c->restart && !ctx->decomp_all_current) return GC_OK;
+        if (c->restart) LAUNCH(ctx, k_decomp_stamp_all, (ctx->n + 255) / 256, 256, ctx->hp);
+        ctx->decomp_all_current = true;
     }
     plan_and_rebuild(ctx, 0.0);
 
@@ -2223,6 +2233,7 @@ int gc_decomp_step_compute(gc_ctx *ctx)
         return fail(ctx, GC_ERR_STATE, "decomposed runs: fixed timestep, no skin, no contact map");
     }
     if (ctx->params_dirty || ctx->topo_dirty) return fail(ctx, GC_ERR_STATE, "call gc_run(steps = 0) first");
+    ctx->decomp_all_current = false;
     launch_rebuild(ctx);
     launch_pair(ctx, 0u, 1);
     LAUNCH(ctx, k_finish<STEP_FUSED>, dim3((P.down_bound + BS - 1) / BS, 1), BS, ctx->hp, 0u, 1);

@@ -311,7 +311,9 @@ int gc_contacts_merge_device(gc_ctx *ctx, const uint64_t *keys_in, const uint32_
    trajectory is bit-identical to the single-GPU one for every world size.  Fixed timestep,
    no skin, no contact map.  Positions on one rank are only partly current afterwards: merge
    the ranks with gc_decomp_owned + gc_get_positions.  gc_run(steps = 0, restart = 0)
-   refreshes parameters mid-run without touching the grid.  world = 1 switches it off.
+   refreshes parameters mid-run without touching the grid.  Resuming a checkpoint: all N
+   positions, gc_run(steps = 0, restart = 1), gc_set_context, gc_set_step (re-stamps every bead
+   as current), gc_run(steps = 0, restart = 0) (re-plans the grid for the loaded context).  world = 1 switches it off.
    Errors (reported by the next synchronising call): GC_ERR_STATE when a bonded partner, or a
    bead after one step, lies outside the halo or a slab is thinner than the halo;
    GC_ERR_CAPACITY when a halo buffer overflows. */

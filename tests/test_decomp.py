@@ -167,3 +167,40 @@ def test_decomposed_context_rejects_plain_run_and_reports_a_thin_halo():
             r.get_positions(0)
     for r in ranks:
         r.close()
+
+
+@pytest.mark.gpu
+def test_decomposed_run_resumes_from_a_checkpoint():
+    """(positions merged from the ranks, context, step) saved mid-run and loaded into FRESH
+    decomposed contexts continues bit for bit: gc_set_step re-stamps every bead as current."""
+    n, world = 60_000, 3
+    semi = tuple(s * (n / 1e5) ** (1 / 3) for s in (5.0, 4.0, 3.0))
+    cfg = synth.InterphaseConfig(wall_semiaxes_init=semi, nucleolus_droplet_energy=0.0,
+                                 wall_semiaxes_spring=(3e4 * n / 60672,) * 3)
+    d, x = synth.make_polymer(n, seed=4, semiaxes=semi)
+    ref = _polymer_rank(d, x, cfg)
+    ref.run(40, cfg.timestep, restart=True)
+    xr = ref.get_positions(0)
+    ref.close()
+
+    ranks = [_polymer_rank(d, x, cfg) for _ in range(world)]
+    ex = decomp.LocalExchange(ranks, halo_layers=3, peer=True)
+    ex.begin(cfg.timestep)
+    ex.step(25)
+    xa, ca = ex.gather_positions(), ranks[0].get_context(0)
+    for g in ranks:
+        g.close()
+
+    ranks = [_polymer_rank(d, xa, cfg) for _ in range(world)]
+    ex = decomp.LocalExchange(ranks, halo_layers=3, peer=True)
+    ex.begin(cfg.timestep)                                   # restart: epoch 1, as in the first run
+    for g in ranks:
+        g.set_context(time=ca.time, semiaxes=list(ca.semiaxes), core_scale=ca.core_scale,
+                      bond_scale=ca.bond_scale, contact_distance=ca.contact_distance)
+        g.set_step(25)
+        g.run(0, cfg.timestep, restart=False)                # the grid follows the loaded context
+    ex.step(15)
+    np.testing.assert_array_equal(ex.gather_positions(), xr)
+    assert ranks[1].get_context(0).step == 40
+    for g in ranks:
+        g.close()
