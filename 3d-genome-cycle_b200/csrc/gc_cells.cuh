@@ -67,15 +67,18 @@ using CellWarpSmem = CellWarpSmemT<CCAP>;
 #endif
 constexpr int MINBLOCKS_DENSE = GC_DENSE_MINBLOCKS;
 
-// Sum over the S slices of each home bead, in fixed order; valid in lanes < H.
-__device__ __forceinline__ void cell_fold(int H, int S, int lane, float &fx, float &fy, float &fz)
+// Sum over the S slices of each home bead (lane = slice * H + home bead), as a fixed binary
+// tree over the slices: ceil(log2 S) rounds instead of S - 1; valid in lanes < H.
+__device__ __forceinline__ void cell_fold(int H, int S, int sl, float &fx, float &fy, float &fz)
 {
-    for (int k = 1; k < S; k++) {
-        const int src = (lane + k * H) & 31;
-        const float gx = __shfl_sync(0xffffffffu, fx, src);
-        const float gy = __shfl_sync(0xffffffffu, fy, src);
-        const float gz = __shfl_sync(0xffffffffu, fz, src);
-        if (lane < H) { fx += gx; fy += gy; fz += gz; }
+    // (sl = slice of this lane; lanes >= H * S carry zeros and never add)
+    int step = 1;
+    while (step < S) step <<= 1;
+    for (step >>= 1; step > 0; step >>= 1) {
+        const float gx = __shfl_down_sync(0xffffffffu, fx, step * H);
+        const float gy = __shfl_down_sync(0xffffffffu, fy, step * H);
+        const float gz = __shfl_down_sync(0xffffffffu, fz, step * H);
+        if (sl < step && sl + step < S) { fx += gx; fy += gy; fz += gz; }
     }
 }
 
@@ -385,7 +388,7 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
             for (int j = 0; j < HB; j++) {
                 float fx = -(hm.ax[j].x + hm.ax[j].y), fy = -(hm.ay[j].x + hm.ay[j].y);
                 float fz = -(hm.az[j].x + hm.az[j].y);
-                cell_fold(H2, S, lane, fx, fy, fz);
+                cell_fold(H2, S, sl, fx, fy, fz);
                 if (lane < H2 && HB * lane + j < ng) pforce[h0 + g0 + HB * lane + j] = make_float4(fx, fy, fz, 0.0f);
             }
         }
