@@ -199,10 +199,11 @@ __device__ __forceinline__ T pair_ld(const T *p)
 }
 
 // All home cells of replica r that this warp gets hold of: from the shared work queue
-// (PERSIST = false: atomic claims, any number of blocks) or a static share of it
-// (PERSIST = true: warp `slot` of `nslots`, one block per replica).  The arithmetic per home
+// (STATIC = false: atomic claims) or a static share of it (STATIC = true: warp `slot` of
+// `nslots` takes cells slot, slot + nslots, ...).  NC selects the read-only load path (false when
+// the arrays are rewritten inside the same kernel).  The arithmetic per home
 // cell -- staging order, culling, lane split, fold -- is the same either way.
-template<bool PLAIN, bool PERSIST>
+template<bool PLAIN, bool STATIC, bool NC>
 __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st, int r, PairUnit *tile, int lane,
                                                    int slot, int nslots)
 {
@@ -235,7 +236,7 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
         // descriptor -> row starts (three L2 round trips) is paid once per claim, and the
         // loads of the second cell are in flight while the first is evaluated.
         int kk0 = 0;
-        if (PERSIST) {
+        if (STATIC) {
             // one block owns the replica: warp `slot` of `nslots` takes cells slot, slot + nslots, ...
             kk0 = next_cell;
             next_cell += nslots * TICKET;
@@ -246,21 +247,21 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
         if (kk0 >= nused) break;
         // (scalars, not arrays: the second cell's five values stay in registers)
         const int kA_ = kk0, kB_ = min(kk0 + 1, nused - 1);
-        const int4 cellA = pair_ld<!PERSIST>(&cells[kA_ < nheavy ? kA_ : P.n - 1 - (kA_ - nheavy)]);
+        const int4 cellA = pair_ld<NC>(&cells[kA_ < nheavy ? kA_ : P.n - 1 - (kA_ - nheavy)]);
         int4 cellB = cellA;
-        if (TICKET == 2) cellB = pair_ld<!PERSIST>(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
+        if (TICKET == 2) cellB = pair_ld<NC>(&cells[kB_ < nheavy ? kB_ : P.n - 1 - (kB_ - nheavy)]);
         int loA = 0, u1A = 0, loB = 0, u1B = 0;
         if (lane < 9) {
             // slots -> the layer-relative unit space of the pair-interleaved copy (unit_slot)
             const int LA = cellA.w + lane / 3 - 1;
-            const int sA = unit_slot(0, LA, pair_ld<!PERSIST>(&start[LA * dxy]));
-            loA = pair_ld<!PERSIST>(&start[cellA.x + row_rel]) + sA;
-            u1A = (pair_ld<!PERSIST>(&start[cellA.x + row_rel + 3]) + sA + 1) >> 1;
+            const int sA = unit_slot(0, LA, pair_ld<NC>(&start[LA * dxy]));
+            loA = pair_ld<NC>(&start[cellA.x + row_rel]) + sA;
+            u1A = (pair_ld<NC>(&start[cellA.x + row_rel + 3]) + sA + 1) >> 1;
             if (TICKET == 2) {
                 const int LB = cellB.w + lane / 3 - 1;
-                const int sB = unit_slot(0, LB, pair_ld<!PERSIST>(&start[LB * dxy]));
-                loB = pair_ld<!PERSIST>(&start[cellB.x + row_rel]) + sB;
-                u1B = (pair_ld<!PERSIST>(&start[cellB.x + row_rel + 3]) + sB + 1) >> 1;
+                const int sB = unit_slot(0, LB, pair_ld<NC>(&start[LB * dxy]));
+                loB = pair_ld<NC>(&start[cellB.x + row_rel]) + sB;
+                u1B = (pair_ld<NC>(&start[cellB.x + row_rel + 3]) + sB + 1) >> 1;
             }
         }
         int h0 = cellA.y, nhome = cellA.z, lo = loA, u1 = u1A;
@@ -300,7 +301,7 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
             // the shifted coordinates order like the floats: one REDUX per bound.
             float2 blx, bly, blz, bhx, bhy, bhz;
             {
-                const float4 hp = pair_ld<!PERSIST>(&sp[h0 + g0 + min(lane, ng - 1)]);
+                const float4 hp = pair_ld<NC>(&sp[h0 + g0 + min(lane, ng - 1)]);
                 const unsigned ux = __float_as_uint(hp.x - ox), uy = __float_as_uint(hp.y - oy);
                 const unsigned uz = __float_as_uint(hp.z - oz);
                 float v;
@@ -328,10 +329,10 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
                     row += k >= t ? step : 0;
                 }
                 const int u = k + __shfl_sync(0xffffffffu, shift, row);
-                const float4 a = pair_ld<!PERSIST>(&uxy[u]);
-                float4 b = pair_ld<!PERSIST>(&uzA[u]);
+                const float4 a = pair_ld<NC>(&uxy[u]);
+                float4 b = pair_ld<NC>(&uzA[u]);
                 float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (!PLAIN) bb = pair_ld<!PERSIST>(&uB[u]);
+                if (!PLAIN) bb = pair_ld<NC>(&uB[u]);
                 // distance of both beads of the unit from the box (packed)
                 const float2 x2 = make_float2(a.x, a.y), y2 = make_float2(a.z, a.w), z2 = make_float2(b.x, b.y);
                 const float2 lx = __fadd2_rn(blx, make_float2(-x2.x, -x2.y)), hx = __fadd2_rn(x2, bhx);
@@ -369,11 +370,11 @@ __device__ __forceinline__ void pair_cells_replica(const Params &P, RepState &st
 #pragma unroll
                         for (int j = 0; j < HB; j++) {
                             const int t = h0 + g0 + min(HB * hl + j, ng - 1);
-                            const float4 me = pair_ld<!PERSIST>(&sp[t]);
+                            const float4 me = pair_ld<NC>(&sp[t]);
                             hm.nx[j] = -me.x; hm.ny[j] = -me.y; hm.nz[j] = -me.z;
                             hm.A[j] = hA; hm.B[j] = 0.0f;
                             if (!PLAIN) {
-                                const float2 abi = pair_ld<!PERSIST>(&sab[t]);
+                                const float2 abi = pair_ld<NC>(&sab[t]);
                                 hm.A[j] = hA * abi.x; hm.B[j] = hB * abi.y;
                             }
                         }
@@ -420,7 +421,12 @@ __global__ void __launch_bounds__(CW * 32, MINB) k_pair_cells(const __grid_const
     // replicas round-robin, starting at a different one.
     for (int rr = 0; rr < P.n_rep; rr++) {
         const int r = (blockIdx.x + rr) % P.n_rep;
-        pair_cells_replica<PLAIN, false>(P, P.st[r], r, s_tile[warp], lane, 0, 1);
+#ifdef GC_STATIC_CLAIM
+        pair_cells_replica<PLAIN, true, true>(P, P.st[r], r, s_tile[warp], lane, blockIdx.x * CW + warp,
+                                              gridDim.x * CW);
+#else
+        pair_cells_replica<PLAIN, false, true>(P, P.st[r], r, s_tile[warp], lane, 0, 1);
+#endif
     }
 }
 
