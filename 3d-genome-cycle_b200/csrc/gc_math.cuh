@@ -98,6 +98,11 @@ __device__ __forceinline__ float well_energy(float eps, float k2, float cut2, fl
 __device__ __forceinline__ float bond_force_factor(int kind, float K, float l, float r2)
 {
     if (kind == 1) return -K;
+    // rest length 0 (every interphase bond): K * 0 / r - K = -K exactly, and r <= 0 only at
+    // r = 0 -- the same bits without the square root and the division
+#ifndef GC_NO_BOND_SHORTCUT
+    if (l == 0.0f) return r2 > 0.0f ? -K : 0.0f;
+#endif
     float r1 = sqrtf(r2);
     if (kind == 0 ? (r1 <= l) : (r1 == 0.0f)) return 0.0f;
     return K * l / r1 - K;
