@@ -548,6 +548,24 @@ def run_b200_arm(args):
             ijv = ens.keys_to_ijv(keys, counts) if rank == 0 else None
             g.synchronize()
             t_map = time.perf_counter() - t2
+            # compartment observables of the merged map on the device (rank 0): binned matrix,
+            # PC1 by power iteration, A/B enrichment (src/pc1.py:21-125)
+            comp[0] = None
+            if rank == 0:
+                try:
+                    t3 = time.perf_counter()
+                    binned.clear()
+                    binned.add_runs(keys, counts)
+                    pc = binned.pc1()
+                    enr = binned.type_enrichment(bin_type, 2, min_separation=2)
+                    comp[0] = {"bins": int(n_bins), "beads_per_bin": BIN, "pc1_explained_variance": float(pc["evr"]),
+                               "pc1_vs_A_fraction_corr": float(abs(np.corrcoef(
+                                   np.nan_to_num(pc["pc1"]), frac_a)[0, 1])),
+                               "contacts_per_bin_pair": {"AA": float(enr[0, 0]), "AB": float(enr[0, 1]),
+                                                         "BB": float(enr[1, 1])},
+                               "ms_outside_timed_region": (time.perf_counter() - t3) * 1e3}
+                except Exception as ex:            # an output product: never take the bench down
+                    comp[0] = {"error": repr(ex)[:200]}
             g.contacts_clear()
             barrier()
             tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local}")
@@ -562,9 +580,27 @@ def run_b200_arm(args):
             bead_chain[s_:e_] = c_
         obs_dev = gc_b200.Observables(len(design.chains), [(k, k + 1) for k in range(len(design.chains))], local)
         obs_dev.set_bead_map(np.maximum(bead_chain, 0), bead_chain)
+        # bins of BIN beads inside every chain (nucleolar beads dropped), typed A / B by majority
+        BIN, n_bins, ranges_b = 50, 0, []
+        bead_bin = np.full(n, -1, dtype=np.int32)
+        for s_, e_ in design.chains:
+            k_ = -(-(e_ - s_) // BIN)
+            bead_bin[s_:e_] = n_bins + (np.arange(e_ - s_) // BIN)
+            ranges_b.append((n_bins, n_bins + k_))
+            n_bins += k_
+        ok_ = bead_bin >= 0
+        frac_a = np.bincount(bead_bin[ok_], weights=(design.a > design.b)[ok_].astype(np.float64), minlength=n_bins) / \
+            np.maximum(np.bincount(bead_bin[ok_], minlength=n_bins), 1)
+        bin_type = np.where(frac_a > 0.5, 0, 1).astype(np.int32)
+        binned = gc_b200.Observables(n_bins, ranges_b, local) if rank == 0 else None
+        if binned is not None:
+            binned.set_bead_map(bead_bin, bead_chain)
+        comp = [None]
         e2e_pass(1)                       # untimed: page-locked staging buffers, NCCL channels
         dt, t_reduce, lap, energy, ctxs, obs, ijv, tot, t_map = e2e_pass(args.steps)
         obs_dev.close()
+        if binned is not None:
+            binned.close()
         e2e = {"value": world * R * n * S * args.steps / dt, "unit": "bead-steps/s",
                "h2d_bytes_per_step": R * n * 12,
                "d2h_bytes_per_step": R * n * 12 + R * 14 * 8 + R * 8,
@@ -596,6 +632,7 @@ def run_b200_arm(args):
                 "rg_mean": float(np.sqrt(obs[:-1] / obs[-1]).mean()),
                 "P_s": {str(sep): float(ps[sep]) for sep in (1, 2, 5, 10, 30, 100, 300, 1000)},
                 "P_s_matches_merged_map": bool(np.array_equal(ps[1:], ps_host[1:])),
+                "compartments": comp[0],
             }
 
     # ---- one cell per GPU over the whole window (configs[0] as written) -----------
